@@ -1,0 +1,227 @@
+/*
+ * paths_b200.h -- C ABI of the B200-native render hot path of rynorris/paths.
+ *
+ * The reference is a monolithic Rust binary with no FFI seam (Cargo.toml has no [lib]); the seam the hot
+ * path sits behind is the public API of `Renderer` (src/renderer.rs:33-141) plus the per-ray query
+ * `BVH::find_intersection` (src/bvh.rs:78).  Every entry point below names the reference item it replaces.
+ * INTEGRATION.md shows the Rust `extern "C"` block a maintainer would add on the reference side.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; all bulk buffers are caller-allocated HOST memory unless the name says
+ *     `device`; the library copies what it keeps.
+ *   - every function returns paths_status (0 = OK) and never unwinds; paths_last_error() returns a
+ *     thread-local message for the last failure (the reference panics instead: renderer.rs:88,107-109).
+ *   - handles are not thread-safe: one caller thread per renderer, like `&mut self` on Renderer.
+ *   - there is no CPU fallback: without a CUDA device every compute entry point fails with PATHS_ERR_CUDA.
+ */
+#ifndef PATHS_B200_H
+#define PATHS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    PATHS_OK = 0,
+    PATHS_ERR_INVALID_ARG = 1,
+    PATHS_ERR_IO = 2,
+    PATHS_ERR_PARSE = 3,
+    PATHS_ERR_CUDA = 4,
+    PATHS_ERR_UNSUPPORTED = 5,
+    PATHS_ERR_INTERNAL = 6
+} paths_status;
+
+#define PATHS_MISS 0xFFFFFFFFu
+
+/* ------------------------------------------------------------------ scene description
+ * What src/serde.rs:65-74 deserialises (SceneDescription), flattened to C arrays. */
+
+typedef struct {
+    uint32_t n_vertices;
+    uint32_t n_faces;
+    const double *vertices;       /* n_vertices x 3; loaders deliver f32-rounded values like tobj / ply-rs */
+    const uint32_t *faces;        /* n_faces x 3 (src/model.rs:105-114) */
+    const double *vertex_colours; /* n_vertices x 3 in [0,1] or NULL (src/ply.rs:59-71) */
+} paths_model_desc;
+
+enum { PATHS_MAT_LAMBERTIAN = 0, PATHS_MAT_MIRROR = 1, PATHS_MAT_GLOSS = 2, PATHS_MAT_COOK_TORRANCE = 3, PATHS_MAT_FRESNEL = 4 };
+
+typedef struct {
+    int32_t type;        /* PATHS_MAT_* (src/material.rs:22-28) */
+    int32_t albedo_mode; /* 0 = static rgb, 1 = per-vertex colour (src/material.rs:168-172) */
+    double albedo[3];
+    double reflectance; /* Gloss r0 (src/material.rs:282-300) */
+    double metalness;   /* Gloss */
+    double roughness;   /* CookTorrance m (src/material.rs:423-434) */
+} paths_basic_material;
+
+typedef struct {
+    paths_basic_material m;    /* m.type == PATHS_MAT_FRESNEL selects diffuse/specular below */
+    double refractive_index;   /* Fresnel (src/material.rs:373-387) */
+    paths_basic_material diffuse;
+    paths_basic_material specular;
+} paths_material_desc;
+
+typedef struct {
+    int32_t shape;          /* 0 = Sphere, 1 = Mesh; one entry per loaded sub-model (src/serde.rs:91-142) */
+    int32_t model;          /* Mesh: index into models */
+    int32_t smooth_normals; /* src/serde.rs:243-252 (default true) */
+    int32_t _pad;
+    double center[3];       /* Sphere */
+    double radius;
+    double translation[3];  /* Mesh instance (src/geom.rs:98-122) */
+    double rot_pitch, rot_yaw, rot_roll; /* YAML values, passed to Matrix3::rotation in the order of serde.rs:103 */
+    double scale;
+    paths_material_desc material;
+} paths_object_desc;
+
+typedef struct {
+    int32_t geometry; /* 0 = Point, 1 = Sphere (src/serde.rs:213-229) */
+    int32_t _pad;
+    double v[3];      /* Point vector, or sphere centre */
+    double radius;
+    double colour[3];
+    double intensity;
+} paths_light_desc;
+
+typedef struct {
+    int32_t type; /* 0 = Flat, 1 = Gradient, 2 = Hdri (src/scene.rs:68-73) */
+    uint32_t width, height;
+    uint32_t _pad;
+    double c0[3];        /* flat colour / overhead colour */
+    double c1[3];        /* horizon colour */
+    const float *texels; /* Hdri: width*height*3 f32 RGB, row-major (src/serde.rs:367-382) */
+} paths_sky_desc;
+
+typedef struct {
+    uint32_t n_models;
+    uint32_t n_objects;
+    uint32_t n_lights;
+    uint32_t _pad;
+    const paths_model_desc *models;
+    const paths_object_desc *objects;
+    const paths_light_desc *lights;
+    paths_sky_desc sky;
+} paths_scene_desc;
+
+/* CameraDescription (src/serde.rs:156-188) */
+typedef struct {
+    uint32_t image_width, image_height;
+    double location[3];
+    double pitch, yaw, roll;
+    double sensor_width, sensor_height, focal_length, focus_distance, aperture;
+} paths_camera;
+
+typedef struct paths_scene paths_scene;
+typedef struct paths_renderer paths_renderer;
+
+/* ------------------------------------------------------------------ options */
+
+enum { PATHS_PRECISION_AUTO = 0, PATHS_PRECISION_F32 = 32, PATHS_PRECISION_F64 = 64 };
+enum { PATHS_SHARD_SAMPLES = 0, PATHS_SHARD_TILES = 1 };
+enum { PATHS_BVH_FAST = 0, PATHS_BVH_REFERENCE = 1 };
+
+typedef struct {
+    int32_t device;        /* CUDA ordinal */
+    int32_t precision;     /* PATHS_PRECISION_*: F32 = production kernels, F64 = parity instantiation */
+    int32_t shard_mode;    /* PATHS_SHARD_* */
+    uint32_t rank, world;  /* this renderer's shard; world = 0 or 1 means unsharded */
+    uint64_t seed;         /* key of the counter-based RNG (the reference's thread_rng is unseedable) */
+    uint32_t max_bounces;  /* trace.rs:14 (10) */
+    uint32_t samples_per_pass; /* camera samples per pixel kept in flight per wavefront pass; 0 = choose */
+    int32_t time_kernels;  /* record CUDA events around every kernel (paths_stats.ms_*) */
+    int32_t _pad;
+} paths_render_opts;
+
+typedef struct {
+    uint64_t samples;      /* camera paths = Renderer::num_rays_cast (src/renderer.rs:75-77,101) */
+    uint64_t extend_rays;  /* closest-hit queries traced (trace.rs:18) */
+    uint64_t shadow_rays;  /* visibility queries traced (trace.rs:61; provably-zero contributions are skipped) */
+    uint64_t bad_samples;  /* Colour::check() would have panicked / unsampleable material (colour.rs:56-60, material.rs:86) */
+    uint64_t kernel_launches;
+    uint64_t passes;
+    double ms_raygen, ms_extend, ms_shade, ms_shadow, ms_accumulate, ms_total; /* valid with time_kernels */
+    uint64_t n_extend_launches, n_shadow_launches;
+} paths_stats;
+
+typedef struct {
+    uint32_t n_prims;           /* flattened items: objects in order (mesh faces in face order), then area lights (scene.rs:143-170) */
+    uint32_t n_triangles, n_spheres;
+    uint32_t n_objects, n_lights;
+    uint32_t ref_nodes, ref_depth;   /* reference-order binary AAC tree (bvh.rs:160-206); 0 until built */
+    uint32_t fast_nodes, fast_depth; /* production wide tree */
+    uint32_t hidden_prims;      /* prims whose own AABB is flat: never hit under bvh.rs:16's strict tmin < tmax */
+    int32_t auto_precision;     /* what PATHS_PRECISION_AUTO resolves to for this scene */
+    double bounds_min[3], bounds_max[3]; /* of prims with radius/extent < 1e5 */
+    double build_ms_ref, build_ms_fast;
+} paths_scene_info;
+
+/* ------------------------------------------------------------------ scene (replaces SceneDescription::scene + Scene::new,
+ * src/serde.rs:81-154, src/scene.rs:143-170; BVH build src/bvh.rs:160-206 runs on the host) */
+
+const char *paths_last_error(void);
+const char *paths_version(void);
+paths_status paths_device_count(int32_t *count);
+
+paths_status paths_scene_create(const paths_scene_desc *desc, paths_scene **out);
+/* YAML -> scene + camera (src/main.rs:43-53).  asset_root may be NULL (paths resolved against the cwd, as the reference does,
+ * then against the YAML's parent directory).  width/height = 0 keep the file's values. */
+paths_status paths_scene_load_yaml(const char *yaml_path, const char *asset_root, uint32_t width, uint32_t height,
+                                   paths_scene **out, paths_camera *camera);
+void paths_scene_destroy(paths_scene *s);
+paths_status paths_scene_get_info(const paths_scene *s, paths_scene_info *info);
+/* per-prim identity as the reference reports it: (is_light, entity id, face index) (bvh.rs T6, geom.rs:48-57) */
+paths_status paths_scene_prim_entity(const paths_scene *s, uint32_t prim, int32_t *is_light, uint32_t *entity, uint32_t *face);
+
+/* BVH::find_intersection over a batch of host rays (src/bvh.rs:78-140).  prim_id = PATHS_MISS and t = +inf on a miss.
+ * precision 64: reference-order binary tree, f64, reference operation order (bit-exact ids and t);
+ * precision 32: production wide tree, f32 triangles / f64 spheres.  bary (n x 3) may be NULL. */
+paths_status paths_trace_closest(paths_scene *s, int32_t device, const double *origins, const double *dirs, size_t n,
+                                 uint32_t *prim_id, double *t, double *bary, int32_t precision);
+
+/* ------------------------------------------------------------------ renderer (replaces Renderer, src/renderer.rs:33-141) */
+
+void paths_render_opts_default(paths_render_opts *o);
+/* Renderer::new(camera, scene, num_workers) (renderer.rs:34-69) */
+paths_status paths_renderer_create(paths_scene *s, const paths_camera *cam, const paths_render_opts *opts, paths_renderer **out);
+/* fill_request_queue + drain_result_queue (renderer.rs:79-110): blocking; advances every owned pixel by spp samples
+ * (sample shard: this rank's share of [done, done+spp) ). */
+paths_status paths_renderer_render(paths_renderer *r, uint32_t spp);
+/* same, without waiting for the device (pair with paths_renderer_sync) */
+paths_status paths_renderer_render_async(paths_renderer *r, uint32_t spp);
+paths_status paths_renderer_sync(paths_renderer *r);
+/* Renderer::render() -> Image (renderer.rs:71-73, pixels.rs:53-79): row-major means, index x + y*W; zero-count pixels are 0 */
+paths_status paths_renderer_image_f32(paths_renderer *r, float *rgb /* W*H*3 */);
+/* Colour::to_bytes + RGB24 pack (colour.rs:30-36,62-74; main.rs:114-120), pitch 3W */
+paths_status paths_renderer_image_rgb24(paths_renderer *r, uint8_t *rgb /* W*H*3 */);
+/* Estimator state (pixels.rs:6-31): W*H x {sum r, sum g, sum b, count} as f64; read for checkpointing or host-side combine */
+paths_status paths_renderer_get_sums(paths_renderer *r, double *sums4 /* W*H*4 */);
+/* adds W*H*4 f64 partial sums into the estimator (combine of shards / resume) */
+paths_status paths_renderer_add_sums(paths_renderer *r, const double *sums4);
+/* device-resident estimator buffer for in-place collectives (NCCL reduce over NVLink): W*H*4 elements of f32 (elem_bytes 4) or f64 (8) */
+paths_status paths_renderer_device_sums(paths_renderer *r, void **device_ptr, size_t *n_elems, int32_t *elem_bytes);
+/* num_rays_cast (renderer.rs:75-77) and friends */
+paths_status paths_renderer_get_stats(paths_renderer *r, paths_stats *st);
+/* set_camera(location, orientation) (renderer.rs:112-120): new epoch; rot is row-major 3x3 */
+paths_status paths_renderer_set_camera(paths_renderer *r, const double location[3], const double rot[9]);
+/* reset() (renderer.rs:122-128) */
+paths_status paths_renderer_reset(paths_renderer *r);
+/* shutdown() (renderer.rs:130-141) */
+void paths_renderer_destroy(paths_renderer *r);
+
+/* Camera::get_ray_for_pixel for sample index S of every pixel of a rectangle, on the device (camera.rs:47-94, worker.rs:58-87).
+ * o, d: n x 3, weight: n (host). */
+paths_status paths_camera_rays(const paths_camera *cam, int32_t device, uint64_t seed, uint32_t sample, uint32_t x0, uint32_t y0,
+                               uint32_t w, uint32_t h, double *o, double *d, double *weight, int32_t precision);
+
+/* image writers for the headless sink (the reference only has an SDL window, main.rs:60-83) */
+paths_status paths_write_ppm(const char *path, const uint8_t *rgb, uint32_t w, uint32_t h);
+paths_status paths_write_pfm(const char *path, const float *rgb, uint32_t w, uint32_t h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

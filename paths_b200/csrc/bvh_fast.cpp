@@ -1,0 +1,291 @@
+// bvh_fast.cpp -- production acceleration structure: binned-SAH binary tree over conservative f32 boxes, leaves of up
+// to 4 primitives, emitted as 64-byte two-child nodes over a leaf-ordered primitive stream.
+//
+// Closest hit does not depend on the shape of the tree (only exact-t ties do), so the production path is free
+// to use a better tree than the reference's AAC build (src/bvh.rs:160-343), whose morton scale collapses whenever a scene
+// holds a 1e6-radius "plane" sphere (src/bvh.rs:178-182).  One reference behaviour does depend on the boxes and is kept:
+// a primitive whose own AABB is flat along an axis can never pass the strict `tmin < tmax` slab test of its leaf
+// (src/bvh.rs:16) and is therefore invisible; such primitives are left out of this tree.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <thread>
+
+#include "host_scene.h"
+
+namespace paths {
+namespace {
+
+struct FBox {
+    float lo[3], hi[3];
+    void reset() {
+        for (int i = 0; i < 3; i++) {
+            lo[i] = std::numeric_limits<float>::infinity();
+            hi[i] = -std::numeric_limits<float>::infinity();
+        }
+    }
+    void grow(const FBox &b) {
+        for (int i = 0; i < 3; i++) {
+            lo[i] = std::min(lo[i], b.lo[i]);
+            hi[i] = std::max(hi[i], b.hi[i]);
+        }
+    }
+    float half_area() const {
+        float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+        return dx * dy + dy * dz + dz * dx;
+    }
+};
+
+inline float round_down(double v) {
+    float f = (float)v;
+    return ((double)f > v) ? std::nextafterf(f, -std::numeric_limits<float>::infinity()) : f;
+}
+inline float round_up(double v) {
+    float f = (float)v;
+    return ((double)f < v) ? std::nextafterf(f, std::numeric_limits<float>::infinity()) : f;
+}
+
+struct Ref {
+    FBox box;
+    float c[3];
+    uint32_t prim;
+};
+
+struct SNode {
+    FBox box;
+    int32_t left, right;
+    uint32_t first, count; // leaf iff count > 0
+};
+
+const int kBins = 16;
+const uint32_t kMaxLeaf = 4;
+const float kTraversalCost = 1.0f, kPrimCost = 1.2f;
+
+struct Sah {
+    std::vector<Ref> refs;
+    std::vector<SNode> nodes; // each task owns a private vector; spliced by the caller
+
+    // builds refs[lo, hi) into `out`, returns local root index
+    static int build(std::vector<Ref> &refs, size_t lo, size_t hi, std::vector<SNode> &out, int depth) {
+        SNode node;
+        node.box.reset();
+        FBox cb;
+        cb.reset();
+        for (size_t i = lo; i < hi; i++) {
+            node.box.grow(refs[i].box);
+            for (int a = 0; a < 3; a++) {
+                cb.lo[a] = std::min(cb.lo[a], refs[i].c[a]);
+                cb.hi[a] = std::max(cb.hi[a], refs[i].c[a]);
+            }
+        }
+        size_t count = hi - lo;
+        node.left = node.right = -1;
+        node.first = (uint32_t)lo;
+        node.count = 0;
+        int me = (int)out.size();
+        out.push_back(node);
+        if (count == 1) {
+            out[me].count = 1;
+            return me;
+        }
+        // binned SAH over the three axes
+        float best_cost = std::numeric_limits<float>::infinity();
+        int best_axis = -1, best_bin = -1;
+        for (int axis = 0; axis < 3; axis++) {
+            float ext = cb.hi[axis] - cb.lo[axis];
+            if (!(ext > 0.0f)) continue;
+            FBox bb[kBins];
+            uint32_t bc[kBins];
+            for (int b = 0; b < kBins; b++) {
+                bb[b].reset();
+                bc[b] = 0;
+            }
+            float k = (float)kBins / ext;
+            for (size_t i = lo; i < hi; i++) {
+                int b = std::min(kBins - 1, std::max(0, (int)((refs[i].c[axis] - cb.lo[axis]) * k)));
+                bb[b].grow(refs[i].box);
+                bc[b]++;
+            }
+            float right_area[kBins];
+            FBox acc;
+            acc.reset();
+            for (int b = kBins - 1; b > 0; b--) {
+                acc.grow(bb[b]);
+                right_area[b] = acc.half_area();
+            }
+            acc.reset();
+            uint32_t nl = 0;
+            for (int b = 0; b < kBins - 1; b++) {
+                acc.grow(bb[b]);
+                nl += bc[b];
+                uint32_t nr = (uint32_t)count - nl;
+                if (nl == 0 || nr == 0) continue;
+                float cost = acc.half_area() * (float)nl + right_area[b + 1] * (float)nr;
+                if (cost < best_cost) {
+                    best_cost = cost;
+                    best_axis = axis;
+                    best_bin = b;
+                }
+            }
+        }
+        size_t mid;
+        if (best_axis >= 0) {
+            float leaf_cost = kPrimCost * (float)count;
+            float split_cost = kTraversalCost + kPrimCost * best_cost / std::max(node.box.half_area(), 1e-30f);
+            if (count <= kMaxLeaf && leaf_cost <= split_cost) {
+                out[me].count = (uint32_t)count;
+                return me;
+            }
+            float ext = cb.hi[best_axis] - cb.lo[best_axis];
+            float k = (float)kBins / ext;
+            float clo = cb.lo[best_axis];
+            Ref *p = std::partition(refs.data() + lo, refs.data() + hi, [&](const Ref &r) {
+                int b = std::min(kBins - 1, std::max(0, (int)((r.c[best_axis] - clo) * k)));
+                return b <= best_bin;
+            });
+            mid = (size_t)(p - refs.data());
+            if (mid == lo || mid == hi) mid = lo + count / 2;
+        } else {
+            // all centroids coincide
+            if (count <= kMaxLeaf) {
+                out[me].count = (uint32_t)count;
+                return me;
+            }
+            mid = lo + count / 2;
+        }
+        if (depth < 3 && count > 65536) {
+            std::vector<SNode> lout, rout;
+            int lroot = 0, rroot = 0;
+            std::thread tl([&] { lroot = build(refs, lo, mid, lout, depth + 1); });
+            rroot = build(refs, mid, hi, rout, depth + 1);
+            tl.join();
+            int lbase = (int)out.size();
+            for (SNode n : lout) {
+                if (n.count == 0) {
+                    n.left += lbase;
+                    n.right += lbase;
+                }
+                out.push_back(n);
+            }
+            int rbase = (int)out.size();
+            for (SNode n : rout) {
+                if (n.count == 0) {
+                    n.left += rbase;
+                    n.right += rbase;
+                }
+                out.push_back(n);
+            }
+            out[me].left = lbase + lroot;
+            out[me].right = rbase + rroot;
+        } else {
+            int l = build(refs, lo, mid, out, depth + 1);
+            int r = build(refs, mid, hi, out, depth + 1);
+            out[me].left = l;
+            out[me].right = r;
+        }
+        return me;
+    }
+};
+
+inline int32_t leaf_code(uint32_t first, uint32_t count) { return ~(int32_t)((first << 3) | (count - 1)); }
+
+uint32_t emit2(const std::vector<SNode> &sn, int node, FastTree &out, int32_t &code) {
+    const SNode &n = sn[node];
+    if (n.count > 0) {
+        code = leaf_code(n.first, n.count);
+        return 1;
+    }
+    int32_t me = (int32_t)out.nodes.size();
+    out.nodes.push_back(FastNode2());
+    code = me;
+    int32_t lc, rc;
+    uint32_t dl = emit2(sn, n.left, out, lc);
+    uint32_t dr = emit2(sn, n.right, out, rc);
+    FastNode2 &fn = out.nodes[me];
+    const FBox &lb = sn[n.left].box, &rb = sn[n.right].box;
+    for (int a = 0; a < 3; a++) {
+        fn.c0[2 * a] = lb.lo[a];
+        fn.c0[2 * a + 1] = lb.hi[a];
+        fn.c1[2 * a] = rb.lo[a];
+        fn.c1[2 * a + 1] = rb.hi[a];
+    }
+    fn.i0 = lc;
+    fn.i1 = rc;
+    fn.pad[0] = fn.pad[1] = 0;
+    return 1 + std::max(dl, dr);
+}
+
+} // namespace
+
+bool build_fast_tree(const HostScene &s, FastTree &out, std::string &err) {
+    std::vector<Ref> refs;
+    refs.reserve(s.prims.size());
+    for (size_t i = 0; i < s.prims.size(); i++) {
+        const HostPrim &p = s.prims[i];
+        if (p.type == 1 && (p.box.lo.x == p.box.hi.x || p.box.lo.y == p.box.hi.y || p.box.lo.z == p.box.hi.z)) continue; // invisible (header)
+        Ref r;
+        r.box.lo[0] = round_down(p.box.lo.x); r.box.lo[1] = round_down(p.box.lo.y); r.box.lo[2] = round_down(p.box.lo.z);
+        r.box.hi[0] = round_up(p.box.hi.x); r.box.hi[1] = round_up(p.box.hi.y); r.box.hi[2] = round_up(p.box.hi.z);
+        if (p.type == 1) {
+            // the f32 kernel intersects f32-rounded vertices: make the box cover them as well
+            const D3 *vs[3] = {&p.a, &p.b, &p.c};
+            for (int k = 0; k < 3; k++) {
+                float fx = (float)vs[k]->x, fy = (float)vs[k]->y, fz = (float)vs[k]->z;
+                r.box.lo[0] = std::min(r.box.lo[0], fx); r.box.hi[0] = std::max(r.box.hi[0], fx);
+                r.box.lo[1] = std::min(r.box.lo[1], fy); r.box.hi[1] = std::max(r.box.hi[1], fy);
+                r.box.lo[2] = std::min(r.box.lo[2], fz); r.box.hi[2] = std::max(r.box.hi[2], fz);
+            }
+        }
+        for (int a = 0; a < 3; a++) r.c[a] = 0.5f * r.box.lo[a] + 0.5f * r.box.hi[a];
+        r.prim = (uint32_t)i;
+        refs.push_back(r);
+    }
+    out = FastTree();
+    if (refs.empty()) {
+        // nothing visible: a tree with one empty inner node keeps the kernels branch-free
+        FastNode2 fn;
+        std::memset(&fn, 0, sizeof(fn));
+        for (int a = 0; a < 3; a++) {
+            fn.c0[2 * a] = fn.c1[2 * a] = std::numeric_limits<float>::infinity();
+            fn.c0[2 * a + 1] = fn.c1[2 * a + 1] = -std::numeric_limits<float>::infinity();
+        }
+        fn.i0 = fn.i1 = 0;
+        out.nodes.push_back(fn);
+        out.root = 0;
+        for (int a = 0; a < 6; a++) out.root_box[a] = (a < 3) ? std::numeric_limits<float>::infinity() : -std::numeric_limits<float>::infinity();
+        out.depth = 1;
+        (void)err;
+        return true;
+    }
+    std::vector<SNode> sn;
+    sn.reserve(refs.size());
+    int root = Sah::build(refs, 0, refs.size(), sn, 0);
+    out.leaf_prims.resize(refs.size());
+    for (size_t i = 0; i < refs.size(); i++) out.leaf_prims[i] = refs[i].prim;
+    out.nodes.reserve(refs.size());
+    out.depth = emit2(sn, root, out, out.root);
+    for (int a = 0; a < 3; a++) {
+        out.root_box[a] = sn[root].box.lo[a];
+        out.root_box[3 + a] = sn[root].box.hi[a];
+    }
+    if (out.root < 0) {
+        // a single leaf: wrap it in one inner node whose second child is empty
+        FastNode2 fn;
+        std::memset(&fn, 0, sizeof(fn));
+        for (int a = 0; a < 3; a++) {
+            fn.c0[2 * a] = sn[root].box.lo[a];
+            fn.c0[2 * a + 1] = sn[root].box.hi[a];
+            fn.c1[2 * a] = std::numeric_limits<float>::infinity();
+            fn.c1[2 * a + 1] = -std::numeric_limits<float>::infinity();
+        }
+        fn.i0 = out.root;
+        fn.i1 = out.root;
+        out.nodes.push_back(fn);
+        out.root = 0;
+        out.depth = 2;
+    }
+    return true;
+}
+
+} // namespace paths

@@ -1,0 +1,101 @@
+// dev_scene.h -- layout of the scene in HBM and of the wavefront path state (see DESIGN.md "Data layout").
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace paths {
+
+// prim_meta[prim] (prim = index in the reference's flattened item list, src/scene.rs:143-170)
+//   x: bit0 = triangle, bit1 = entity is a light;  y: entity id;  z: face index in its model;  w: unused
+#define PATHS_PM_TRI 1u
+#define PATHS_PM_LIGHT 2u
+
+struct DevObject {          // src/scene.rs:35-40 + src/geom.rs:98-122 + resolved material record
+    int32_t shape, smooth;
+    uint32_t vert_base, face_base;
+    double rot[9];
+    int32_t mat_type, vertex_albedo;
+    double albedo[3];
+    double r0, metalness, roughness;
+    // Fresnel combination, brdf() only
+    int32_t d_type, s_type;
+    double d_albedo[3], s_albedo[3];
+    double d_r0, d_metal, d_rough, s_r0, s_metal, s_rough, fresnel_r0;
+};
+
+struct DevLight { // src/scene.rs:42-66
+    int32_t geometry;
+    uint32_t prim;
+    double v[3];
+    double radius;
+    double colour[3];
+    double intensity;
+};
+
+struct DevRefNode { // reference-order binary tree, child boxes in the parent (src/bvh.rs:23-70)
+    double lbox[6];
+    double rbox[6];
+    int32_t left, right; // >= 0 inner; < 0 leaf: ~prim
+    int32_t pad[2];
+};
+
+struct DevScene {
+    uint32_t n_prims, n_lights, n_objects;
+    // ---- prim-id indexed tables
+    const uint4 *prim_meta;
+    const double *prim_geom; // 12 doubles per prim. triangle: a, b, c, n ; sphere: centre, radius
+    // ---- reference tree (f64 parity kernels)
+    const DevRefNode *ref_nodes;
+    int32_t ref_root;
+    double ref_root_box[6];
+    // ---- production tree (f32 kernels): 4 float4 per node, 3 float4 per leaf slot
+    const float4 *fast_nodes;
+    const float4 *fast_leaves;
+    int32_t fast_root;
+    // ---- shading tables
+    const DevObject *objects;
+    const DevLight *lights;
+    const double *vertex_normals; // 3 per vertex, concatenated over models
+    const double *vertex_colours; // 3 per vertex
+    const uint32_t *faces;        // 3 per face
+    int32_t sky_type;
+    double sky_c0[3], sky_c1[3];
+    uint32_t sky_w, sky_h;
+    const float *sky_texels;
+};
+
+struct DevCamera { // src/camera.rs:12-27 after CameraDescription::to_camera (src/serde.rs:172-188)
+    uint32_t width, height;
+    double location[3];
+    double rot[9];
+    double sensor_width, sensor_height, focal_length, distance_from_lens, aperture;
+};
+
+// One wavefront pass keeps n_slots camera paths in flight.  Slot i carries sample (s_base + i / n_local) of local pixel
+// (i % n_local).  Path state stays in its slot for the whole pass; queues hold slot indices.
+template <typename R4> struct PathState {
+    R4 *ray_o; // origin xyz
+    R4 *ray_d; // direction xyz
+    R4 *hit;   // prim bits, t, bx, by
+    R4 *thr;   // throughput rgb, w = flags bits: loops | last_bounce_specular << 8
+    R4 *col;   // radiance rgb gathered so far, w = camera weight (src/camera.rs:91)
+    // shadow-ray records, dense by shadow queue position
+    R4 *sh_o;  // origin xyz, w = light index bits
+    R4 *sh_d;  // direction xyz, w = slot bits
+    R4 *sh_c;  // contribution rgb (already multiplied by throughput)
+};
+
+struct PassControl {
+    uint32_t *qcount;    // [max_bounces + 2] live paths entering bounce b
+    uint32_t *scount;    // [max_bounces + 2] shadow rays emitted at bounce b
+    uint32_t *work;      // [3 * (max_bounces + 2)] dynamic-fetch cursors, one per launch
+    uint32_t *queue[2];  // slot indices, ping-pong
+    unsigned long long *totals; // [0] extend rays [1] shadow rays [2] bad samples [3] samples
+};
+
+struct ShardInfo {
+    uint32_t n_local;         // pixels owned by this rank
+    const uint32_t *pixels;   // local -> global pixel index, or NULL for identity
+};
+
+} // namespace paths

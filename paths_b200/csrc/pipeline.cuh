@@ -1,0 +1,334 @@
+// pipeline.cuh -- the wavefront kernels: raygen -> { extend -> shade -> shadow } x (max_bounces + 1) -> accumulate.
+//
+// Replaces the reference's thread pool (src/renderer.rs:34-110, src/worker.rs:43-87) and the per-path loop of
+// trace_ray (src/trace.rs:7-121).  One pass advances n_slots camera paths in lock step; path state lives in SoA
+// arrays of 16-byte (f32) / 32-byte (f64) records indexed by slot; live slots and shadow rays are compacted into
+// queues with one ballot + popc + atomicAdd per warp.  All kernels are persistent: a fixed grid of warps pulls
+// batches of 32 queue entries through an atomic cursor, so no host round trip is needed to learn queue lengths.
+#pragma once
+#include "dev_shade.cuh"
+#include "dev_trace.cuh"
+
+namespace paths {
+
+#define PATHS_FULL_MASK 0xFFFFFFFFu
+#define PATHS_FLAG_SPECULAR 0x100u
+
+template <typename R> struct IsF64 {
+    static const bool value = false;
+};
+template <> struct IsF64<double> {
+    static const bool value = true;
+};
+
+template <typename R> __device__ __forceinline__ typename Vec4T<R>::type ld4(const typename Vec4T<R>::type *p) { return *p; }
+
+__device__ __forceinline__ uint32_t warp_fetch(uint32_t *cursor) {
+    uint32_t base = 0;
+    if ((threadIdx.x & 31u) == 0) base = atomicAdd(cursor, 32u);
+    return __shfl_sync(PATHS_FULL_MASK, base, 0);
+}
+// position in a queue for every lane with pred set; one atomic per warp
+__device__ __forceinline__ uint32_t warp_append(uint32_t *counter, bool pred) {
+    unsigned m = __ballot_sync(PATHS_FULL_MASK, pred);
+    if (m == 0) return 0;
+    unsigned lane = threadIdx.x & 31u;
+    int leader = __ffs(m) - 1;
+    uint32_t base = 0;
+    if ((int)lane == leader) base = atomicAdd(counter, (uint32_t)__popc(m));
+    base = __shfl_sync(PATHS_FULL_MASK, base, leader);
+    return base + __popc(m & ((1u << lane) - 1u));
+}
+
+// ------------------------------------------------------------------ raygen (src/worker.rs:58-87, src/camera.rs:47-94)
+template <typename R>
+__global__ void __launch_bounds__(256) k_raygen(DevCamera cam, uint32_t k0, uint32_t k1, ShardInfo shard, uint32_t s_base, uint32_t n_slots,
+                                                PathState<typename Vec4T<R>::type> ps, PassControl pc) {
+    uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += stride) {
+        uint32_t lp = i % shard.n_local, k = i / shard.n_local;
+        uint32_t pixel = shard.pixels ? shard.pixels[lp] : lp;
+        V3<R> o, d;
+        R w;
+        pixel_sample_ray<R>(cam, k0, k1, pixel, s_base + k, o, d, w);
+        ps.ray_o[i] = mk4(o.x, o.y, o.z, R(0));
+        ps.ray_d[i] = mk4(d.x, d.y, d.z, R(0));
+        ps.thr[i] = mk4(R(1), R(1), R(1), bits_to_real(PATHS_FLAG_SPECULAR, R(0))); // trace.rs:8-11
+        ps.col[i] = mk4(R(0), R(0), R(0), w);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) pc.qcount[0] = n_slots;
+}
+
+// ------------------------------------------------------------------ extend: closest hit (src/scene.rs:172-197 -> src/bvh.rs:78-140)
+template <typename R>
+__global__ void __launch_bounds__(128) k_extend(DevScene sc, PathState<typename Vec4T<R>::type> ps, const uint32_t *queue, const uint32_t *count_ptr,
+                                                uint32_t *cursor) {
+    const uint32_t count = *count_ptr;
+    const uint32_t lane = threadIdx.x & 31u;
+    for (;;) {
+        uint32_t base = warp_fetch(cursor);
+        if (base >= count) break;
+        uint32_t i = base + lane;
+        if (i < count) {
+            uint32_t slot = queue ? queue[i] : i;
+            typename Vec4T<R>::type o = ps.ray_o[slot], d = ps.ray_d[slot];
+            if (IsF64<R>::value) {
+                Hit64 h = trace_ref(sc, mk3((double)o.x, (double)o.y, (double)o.z), mk3((double)d.x, (double)d.y, (double)d.z));
+                ps.hit[slot] = mk4(bits_to_real(h.prim, R(0)), R(h.t), R(h.bx), R(h.by));
+            } else {
+                HitF h = trace_fast<false>(sc, (float)o.x, (float)o.y, (float)o.z, (float)d.x, (float)d.y, (float)d.z, __int_as_float(0x7f800000),
+                                           0xFFFFFFFFu);
+                ps.hit[slot] = mk4(bits_to_real(h.prim, R(0)), R(h.t), R(h.bx), R(h.by));
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ shade: one iteration of trace_ray's loop body (src/trace.rs:13-118)
+template <typename R> struct ShadeOut {
+    bool alive, shadow;
+    V3<R> sh_o, sh_d, sh_c;
+    uint32_t light;
+};
+
+template <typename R>
+__device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typename Vec4T<R>::type> &ps, uint32_t slot, uint32_t pixel, uint32_t S,
+                                           uint32_t k0, uint32_t k1, uint32_t max_bounces, unsigned long long *totals, ShadeOut<R> &out) {
+    typedef typename Vec4T<R>::type R4;
+    const V3<R> black = mk3<R>(R(0), R(0), R(0));
+    R4 o4 = ps.ray_o[slot], d4 = ps.ray_d[slot], h4 = ps.hit[slot], t4 = ps.thr[slot], c4 = ps.col[slot];
+    V3<R> ro = mk3<R>(o4.x, o4.y, o4.z), rd = mk3<R>(d4.x, d4.y, d4.z);
+    V3<R> throughput = mk3<R>(t4.x, t4.y, t4.z), colour = mk3<R>(c4.x, c4.y, c4.z);
+    uint32_t flags = real_to_bits(t4.w);
+    uint32_t loops = flags & 0xFFu;
+    bool last_specular = (flags & PATHS_FLAG_SPECULAR) != 0;
+    uint32_t prim = real_to_bits(h4.x);
+    out.alive = false;
+    out.shadow = false;
+
+    if (prim == 0xFFFFFFFFu) { // trace.rs:20-23
+        colour = colour + throughput * sky_light<R>(sc, neg(rd));
+        ps.col[slot] = mk4(colour.x, colour.y, colour.z, c4.w);
+        return;
+    }
+    // ---- Collision (geom.rs:59-70) + Scene::find_intersection post-processing (scene.rs:172-197)
+    const uint4 meta = sc.prim_meta[prim];
+    const double *g = sc.prim_geom + (size_t)prim * 12;
+    R t = h4.y, bx = h4.z, by = h4.w;
+    V3<R> location = ro + (rd * t);
+    V3<R> normal;
+    bool is_tri = (meta.x & PATHS_PM_TRI) != 0;
+    if (is_tri) { // geom.rs:293-302
+        V3<R> n = mk3<R>(R(g[9]), R(g[10]), R(g[11]));
+        R cos_theta = dot(n, rd);
+        normal = cos_theta > R(0) ? neg(n) : n;
+    } else { // geom.rs:228-234
+        normal = normed(location - mk3<R>(R(g[0]), R(g[1]), R(g[2])));
+    }
+    bool is_light = (meta.x & PATHS_PM_LIGHT) != 0;
+    R bz = R(1.0) - bx - by;
+    const DevObject *obj = is_light ? nullptr : sc.objects + meta.y;
+    const uint32_t *face = nullptr;
+    if (obj && obj->shape == 1 && is_tri) {
+        face = sc.faces + 3 * ((size_t)obj->face_base + meta.z);
+        if (obj->smooth) { // model.rs:142-156 (un-normalised, not flipped) then Mesh::rotate (geom.rs:119-121)
+            const double *vn = sc.vertex_normals + 3 * (size_t)obj->vert_base;
+            V3<R> an = mk3<R>(R(vn[3 * face[0]]), R(vn[3 * face[0] + 1]), R(vn[3 * face[0] + 2]));
+            V3<R> bn = mk3<R>(R(vn[3 * face[1]]), R(vn[3 * face[1] + 1]), R(vn[3 * face[1] + 2]));
+            V3<R> cn = mk3<R>(R(vn[3 * face[2]]), R(vn[3 * face[2] + 1]), R(vn[3 * face[2] + 2]));
+            V3<R> sn = an * bx + bn * by + cn * bz;
+            normal = mat_apply<R>(obj->rot, sn);
+        }
+    }
+    R cos_in = dot(rd, neg(normal)); // trace.rs:25-28
+    if (cos_in <= R(0)) return;
+    if (is_light) { // trace.rs:31-41
+        if (last_specular) {
+            const DevLight &l = sc.lights[meta.y];
+            colour = colour + throughput * mk3<R>(R(l.colour[0]), R(l.colour[1]), R(l.colour[2])) * R(l.intensity);
+            if (col_bad(colour)) atomicAdd(totals + 2, 1ull);
+            ps.col[slot] = mk4(colour.x, colour.y, colour.z, c4.w);
+        }
+        return;
+    }
+    // ---- material resolve (trace.rs:44-50, material.rs:39-49,183-195, model.rs:158-172)
+    Material<R> mat = load_material<R>(*obj);
+    if (face && !mat.fresnel && (mat.m.type == 0 || mat.m.type == 2) && obj->vertex_albedo) {
+        const double *vc = sc.vertex_colours + 3 * (size_t)obj->vert_base;
+        V3<R> ac = mk3<R>(R(vc[3 * face[0]]), R(vc[3 * face[0] + 1]), R(vc[3 * face[0] + 2]));
+        V3<R> bc = mk3<R>(R(vc[3 * face[1]]), R(vc[3 * face[1] + 1]), R(vc[3 * face[1] + 2]));
+        V3<R> cc = mk3<R>(R(vc[3 * face[2]]), R(vc[3 * face[2] + 1]), R(vc[3 * face[2] + 2]));
+        mat.m.albedo = ac * bx + bc * by + cc * bz;
+    }
+    U4 r0 = philox4x32_10(pixel, S, loops * 2u, PATHS_TAG_PATH, k0, k1);
+    U4 r1 = philox4x32_10(pixel, S, loops * 2u + 1u, PATHS_TAG_PATH, k0, k1);
+    V3<R> vec_out = neg(rd);
+    V3<R> new_origin = location + normal * R(0.0001); // trace.rs:57,89
+
+    // ---- next event estimation (trace.rs:53-82)
+    if (sc.n_lights > 0) {
+        uint32_t nl = sc.n_lights;
+        uint32_t id = min(nl - 1u, (uint32_t)(u01<R>(r0.v[0]) * R(nl))); // scene.rs:199-206
+        const DevLight &light = sc.lights[id];
+        V3<R> in_dir;
+        R inv_pdf;
+        light_sample<R>(light, location, u01<R>(r0.v[1]), u01<R>(r0.v[2]), in_dir, inv_pdf);
+        V3<R> sdir = neg(in_dir);
+        R cos_theta = fmax_(R(0.0), dot(normal, sdir));
+        if (cos_theta > R(0)) {
+            V3<R> base = mk3<R>(R(light.colour[0]), R(light.colour[1]), R(light.colour[2])) * R(light.intensity);
+            V3<R> brdf = material_brdf<R>(mat, vec_out, neg(sdir), normal);
+            V3<R> direct = base * brdf * inv_pdf;
+            if (col_bad(direct)) atomicAdd(totals + 2, 1ull); // Colour::check (trace.rs:80)
+            V3<R> contrib = direct * throughput;
+            // a zero contribution cannot change the estimate: skip its visibility query
+            if (contrib.x != R(0) || contrib.y != R(0) || contrib.z != R(0)) {
+                out.shadow = true;
+                out.sh_o = new_origin;
+                out.sh_d = sdir;
+                out.sh_c = contrib;
+                out.light = id;
+            }
+        }
+    }
+    // ---- BSDF sampling (trace.rs:84-98)
+    V3<R> direction, brdf;
+    R pdf;
+    bool is_specular;
+    if (!material_sample<R>(mat, vec_out, normal, u01<R>(r0.v[3]), u01<R>(r1.v[0]), u01<R>(r1.v[1]), direction, pdf, brdf, is_specular)) {
+        atomicAdd(totals + 2, 1ull); // the reference panics: "Not implemented" (material.rs:86)
+        return;
+    }
+    V3<R> attenuation = brdf / pdf;
+    throughput = throughput * attenuation;
+    if (cmax3(throughput) <= R(0)) return;
+    // emittance is BLACK for every material the scene schema can build (serde.rs:278-291): trace.rs:100-101 adds zero
+    if (loops >= 2) { // Russian roulette (trace.rs:104-111); survival chance is not clamped to 1
+        R survival = cmax3(throughput);
+        if (u01<R>(r1.v[2]) > survival) return;
+        throughput = throughput / survival;
+    }
+    loops += 1;
+    if (loops > max_bounces) return; // trace.rs:14-16
+    ps.ray_o[slot] = mk4(new_origin.x, new_origin.y, new_origin.z, R(0));
+    ps.ray_d[slot] = mk4(direction.x, direction.y, direction.z, R(0));
+    ps.thr[slot] = mk4(throughput.x, throughput.y, throughput.z, bits_to_real(loops | (is_specular ? PATHS_FLAG_SPECULAR : 0u), R(0)));
+    out.alive = true;
+    (void)black;
+}
+
+template <typename R>
+__global__ void __launch_bounds__(128) k_shade(DevScene sc, PathState<typename Vec4T<R>::type> ps, ShardInfo shard, uint32_t s_base, uint32_t k0,
+                                               uint32_t k1, uint32_t max_bounces, const uint32_t *queue, uint32_t *queue_next,
+                                               const uint32_t *count_ptr, uint32_t *next_count, uint32_t *shadow_count, uint32_t *cursor,
+                                               unsigned long long *totals) {
+    const uint32_t count = *count_ptr;
+    const uint32_t lane = threadIdx.x & 31u;
+    for (;;) {
+        uint32_t base = warp_fetch(cursor);
+        if (base >= count) break;
+        uint32_t i = base + lane;
+        ShadeOut<R> out;
+        out.alive = out.shadow = false;
+        uint32_t slot = 0;
+        if (i < count) {
+            slot = queue ? queue[i] : i;
+            uint32_t lp = slot % shard.n_local, k = slot / shard.n_local;
+            uint32_t pixel = shard.pixels ? shard.pixels[lp] : lp;
+            shade_path<R>(sc, ps, slot, pixel, s_base + k, k0, k1, max_bounces, totals, out);
+        }
+        uint32_t spos = warp_append(shadow_count, out.shadow);
+        if (out.shadow) {
+            ps.sh_o[spos] = mk4(out.sh_o.x, out.sh_o.y, out.sh_o.z, bits_to_real(out.light, R(0)));
+            ps.sh_d[spos] = mk4(out.sh_d.x, out.sh_d.y, out.sh_d.z, bits_to_real(slot, R(0)));
+            ps.sh_c[spos] = mk4(out.sh_c.x, out.sh_c.y, out.sh_c.z, R(0));
+        }
+        uint32_t qpos = warp_append(next_count, out.alive);
+        if (out.alive) queue_next[qpos] = slot;
+    }
+}
+
+// ------------------------------------------------------------------ shadow: visibility of the NEE sample (src/trace.rs:61-66)
+template <typename R>
+__global__ void __launch_bounds__(128) k_shadow(DevScene sc, PathState<typename Vec4T<R>::type> ps, const uint32_t *count_ptr, uint32_t *cursor,
+                                                unsigned long long *totals) {
+    typedef typename Vec4T<R>::type R4;
+    const uint32_t count = *count_ptr;
+    const uint32_t lane = threadIdx.x & 31u;
+    for (;;) {
+        uint32_t base = warp_fetch(cursor);
+        if (base >= count) break;
+        uint32_t i = base + lane;
+        if (i < count) {
+            R4 o = ps.sh_o[i], d = ps.sh_d[i];
+            uint32_t lid = real_to_bits(o.w), slot = real_to_bits(d.w);
+            bool occluded;
+            if (IsF64<R>::value) {
+                // the reference runs a full closest-hit query and compares entities (trace.rs:61-66)
+                Hit64 h = trace_ref(sc, mk3((double)o.x, (double)o.y, (double)o.z), mk3((double)d.x, (double)d.y, (double)d.z));
+                occluded = false;
+                if (h.prim != 0xFFFFFFFFu) {
+                    uint4 m = sc.prim_meta[h.prim];
+                    occluded = !((m.x & PATHS_PM_LIGHT) && m.y == lid);
+                }
+            } else {
+                // same predicate as an any-hit query: occluded <=> some primitive of another entity lies closer than the
+                // nearest hit on the light's own sphere (t_light = inf for point lights, which own no primitive)
+                const DevLight &l = sc.lights[lid];
+                float t_light = __int_as_float(0x7f800000);
+                if (l.geometry == 1) {
+                    double tl;
+                    if (sphere_hit64(mk3(l.v[0], l.v[1], l.v[2]), l.radius, mk3((double)o.x, (double)o.y, (double)o.z),
+                                     mk3((double)d.x, (double)d.y, (double)d.z), tl))
+                        t_light = (float)tl;
+                }
+                HitF h = trace_fast<true>(sc, (float)o.x, (float)o.y, (float)o.z, (float)d.x, (float)d.y, (float)d.z, t_light, l.prim);
+                occluded = h.prim != 0xFFFFFFFFu;
+            }
+            if (!occluded) { // trace.rs:81: colour += direct * throughput
+                R4 c = ps.sh_c[i];
+                R4 col = ps.col[slot];
+                col.x += c.x;
+                col.y += c.y;
+                col.z += c.z;
+                if (col.x < R(0) || col.y < R(0) || col.z < R(0)) atomicAdd(totals + 2, 1ull); // Colour::check (trace.rs:82)
+                ps.col[slot] = col;
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ accumulate (src/pixels.rs:6-31,49-51; worker.rs:76 applies the camera weight)
+template <typename R>
+__global__ void __launch_bounds__(256) k_accumulate(PathState<typename Vec4T<R>::type> ps, ShardInfo shard, uint32_t spp_pass,
+                                                    typename Vec4T<R>::type *sums) {
+    typedef typename Vec4T<R>::type R4;
+    uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t lp = blockIdx.x * blockDim.x + threadIdx.x; lp < shard.n_local; lp += stride) {
+        uint32_t pixel = shard.pixels ? shard.pixels[lp] : lp;
+        R4 s = sums[pixel];
+        for (uint32_t k = 0; k < spp_pass; k++) {
+            R4 c = ps.col[(size_t)k * shard.n_local + lp];
+            s.x += c.x * c.w;
+            s.y += c.y * c.w;
+            s.z += c.z * c.w;
+        }
+        s.w += R(spp_pass);
+        sums[pixel] = s;
+    }
+}
+
+__global__ void k_tally(PassControl pc, uint32_t n_bounces, uint32_t n_slots) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        unsigned long long e = 0, s = 0;
+        for (uint32_t b = 0; b < n_bounces; b++) {
+            e += pc.qcount[b];
+            s += pc.scount[b];
+        }
+        pc.totals[0] += e;
+        pc.totals[1] += s;
+        pc.totals[3] += n_slots;
+    }
+}
+
+} // namespace paths
