@@ -172,6 +172,9 @@ paths_status paths_scene_create(const paths_scene_desc *desc, paths_scene **out)
 paths_status paths_scene_load_yaml(const char *yaml_path, const char *asset_root, uint32_t width, uint32_t height,
                                    paths_scene **out, paths_camera *camera);
 void paths_scene_destroy(paths_scene *s);
+/* construct_bvh_aac (src/bvh.rs:160-206) on the host, ahead of first use: which = PATHS_BVH_REFERENCE builds the reference-order
+ * AAC tree the f64 kernels traverse, PATHS_BVH_FAST the production SAH tree.  Trees are otherwise built lazily. */
+paths_status paths_scene_build_bvh(paths_scene *s, int32_t which);
 paths_status paths_scene_get_info(const paths_scene *s, paths_scene_info *info);
 /* per-prim identity as the reference reports it: (is_light, entity id, face index) (bvh.rs T6, geom.rs:48-57) */
 paths_status paths_scene_prim_entity(const paths_scene *s, uint32_t prim, int32_t *is_light, uint32_t *entity, uint32_t *face);

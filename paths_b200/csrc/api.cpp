@@ -1,0 +1,362 @@
+// api.cpp -- the C ABI of include/paths_b200.h.  No exception crosses this boundary; every failure becomes a
+// paths_status plus a thread-local message.  There is no CPU fallback behind any compute entry point.
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <exception>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime_api.h>
+
+#include "loaders.h"
+#include "scene_device.h"
+
+using namespace paths;
+
+namespace {
+thread_local std::string g_err;
+paths_status fail(paths_status st, const std::string &msg) {
+    g_err = msg;
+    return st;
+}
+double now_ms() {
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+} // namespace
+
+struct paths_scene {
+    HostScene hs;
+    RefTree ref;
+    FastTree fast;
+    bool has_ref = false, has_fast = false;
+    double ms_ref = 0.0, ms_fast = 0.0;
+    struct Staged {
+        SceneDevice *sd;
+        bool ref, fast;
+    };
+    std::vector<Staged> staged;
+    std::mutex mu;
+    ~paths_scene() {
+        for (Staged &s : staged) delete s.sd;
+    }
+};
+
+struct paths_renderer {
+    RendererBase *impl = nullptr;
+    paths_scene *scene = nullptr;
+    uint32_t w = 0, h = 0;
+    ~paths_renderer() { delete impl; }
+};
+
+namespace {
+
+paths_status check_device(int32_t device) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return fail(PATHS_ERR_CUDA, std::string("no CUDA device available (") + (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0") +
+                                        "); this library has no CPU path");
+    if (device < 0 || device >= n) return fail(PATHS_ERR_INVALID_ARG, "device ordinal out of range");
+    return PATHS_OK;
+}
+
+// stages the scene on `device` with the trees the caller needs; builds a missing tree first
+paths_status ensure_staged(paths_scene *s, int device, bool need_ref, bool need_fast, const SceneDevice **out) {
+    std::lock_guard<std::mutex> lock(s->mu);
+    for (paths_scene::Staged &st : s->staged)
+        if (st.sd->device == device && (!need_ref || st.ref) && (!need_fast || st.fast)) {
+            *out = st.sd;
+            return PATHS_OK;
+        }
+    std::string err;
+    if (need_ref && !s->has_ref) {
+        double t0 = now_ms();
+        if (!build_ref_tree(s->hs, s->ref, err)) return fail(PATHS_ERR_UNSUPPORTED, err);
+        s->ms_ref = now_ms() - t0;
+        s->has_ref = true;
+    }
+    if (need_fast && !s->has_fast) {
+        double t0 = now_ms();
+        if (!build_fast_tree(s->hs, s->fast, err)) return fail(PATHS_ERR_INTERNAL, err);
+        s->ms_fast = now_ms() - t0;
+        s->has_fast = true;
+    }
+    SceneDevice *sd = upload_scene(device, s->hs, s->has_ref ? &s->ref : nullptr, s->has_fast ? &s->fast : nullptr, err);
+    if (!sd) return fail(PATHS_ERR_CUDA, err);
+    s->staged.push_back(paths_scene::Staged{sd, s->has_ref, s->has_fast});
+    *out = sd;
+    return PATHS_OK;
+}
+
+int resolve_precision(const paths_scene *s, int32_t precision) {
+    if (precision == PATHS_PRECISION_F32 || precision == PATHS_PRECISION_F64) return precision;
+    return s->hs.auto_precision;
+}
+
+} // namespace
+
+#define PATHS_GUARD_BEGIN try {
+#define PATHS_GUARD_END                                                       \
+    }                                                                         \
+    catch (const std::bad_alloc &) { return fail(PATHS_ERR_INTERNAL, "out of host memory"); } \
+    catch (const std::exception &e) { return fail(PATHS_ERR_INTERNAL, e.what()); }            \
+    catch (...) { return fail(PATHS_ERR_INTERNAL, "unknown exception"); }
+
+extern "C" {
+
+const char *paths_last_error(void) { return g_err.c_str(); }
+const char *paths_version(void) { return "paths_b200 0.1 (sm_100a)"; }
+
+paths_status paths_device_count(int32_t *count) {
+    if (!count) return fail(PATHS_ERR_INVALID_ARG, "null count");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) {
+        *count = 0;
+        return fail(PATHS_ERR_CUDA, cudaGetErrorString(e));
+    }
+    *count = n;
+    return PATHS_OK;
+}
+
+paths_status paths_scene_create(const paths_scene_desc *desc, paths_scene **out) {
+    PATHS_GUARD_BEGIN
+    if (!desc || !out) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    *out = nullptr;
+    if ((desc->n_models && !desc->models) || (desc->n_objects && !desc->objects) || (desc->n_lights && !desc->lights))
+        return fail(PATHS_ERR_INVALID_ARG, "scene description has a count without its array");
+    paths_scene *s = new paths_scene();
+    std::string err;
+    if (!build_host_scene(*desc, s->hs, err)) {
+        delete s;
+        return fail(PATHS_ERR_INVALID_ARG, err);
+    }
+    *out = s;
+    return PATHS_OK;
+    PATHS_GUARD_END
+}
+
+paths_status paths_scene_load_yaml(const char *yaml_path, const char *asset_root, uint32_t width, uint32_t height, paths_scene **out,
+                                   paths_camera *camera) {
+    PATHS_GUARD_BEGIN
+    if (!yaml_path || !out || !camera) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    *out = nullptr;
+    LoadedScene ls;
+    std::string err;
+    paths_status st = load_scene_yaml(yaml_path, asset_root ? asset_root : "", ls, err);
+    if (st != PATHS_OK) return fail(st, err);
+    if (width) ls.camera.image_width = width;
+    if (height) ls.camera.image_height = height;
+    paths_scene_desc desc;
+    ls.fill_desc(desc);
+    paths_scene *s = new paths_scene();
+    if (!build_host_scene(desc, s->hs, err)) {
+        delete s;
+        return fail(PATHS_ERR_INVALID_ARG, err);
+    }
+    *camera = ls.camera;
+    *out = s;
+    return PATHS_OK;
+    PATHS_GUARD_END
+}
+
+void paths_scene_destroy(paths_scene *s) { delete s; }
+
+paths_status paths_scene_build_bvh(paths_scene *s, int32_t which) {
+    PATHS_GUARD_BEGIN
+    if (!s) return fail(PATHS_ERR_INVALID_ARG, "null scene");
+    std::lock_guard<std::mutex> lock(s->mu);
+    std::string err;
+    if (which == PATHS_BVH_REFERENCE) {
+        if (!s->has_ref) {
+            double t0 = now_ms();
+            if (!build_ref_tree(s->hs, s->ref, err)) return fail(PATHS_ERR_UNSUPPORTED, err);
+            s->ms_ref = now_ms() - t0;
+            s->has_ref = true;
+        }
+    } else if (which == PATHS_BVH_FAST) {
+        if (!s->has_fast) {
+            double t0 = now_ms();
+            if (!build_fast_tree(s->hs, s->fast, err)) return fail(PATHS_ERR_INTERNAL, err);
+            s->ms_fast = now_ms() - t0;
+            s->has_fast = true;
+        }
+    } else return fail(PATHS_ERR_INVALID_ARG, "unknown tree kind");
+    return PATHS_OK;
+    PATHS_GUARD_END
+}
+
+paths_status paths_scene_get_info(const paths_scene *s, paths_scene_info *info) {
+    if (!s || !info) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    std::memset(info, 0, sizeof(*info));
+    info->n_prims = (uint32_t)s->hs.prims.size();
+    info->n_triangles = s->hs.n_tris;
+    info->n_spheres = s->hs.n_spheres;
+    info->n_objects = (uint32_t)s->hs.objects.size();
+    info->n_lights = (uint32_t)s->hs.lights.size();
+    if (s->has_ref) {
+        info->ref_nodes = s->ref.n_nodes_total;
+        info->ref_depth = s->ref.depth;
+    }
+    if (s->has_fast) {
+        info->fast_nodes = (uint32_t)s->fast.nodes.size();
+        info->fast_depth = s->fast.depth;
+    }
+    info->hidden_prims = s->hs.hidden;
+    info->auto_precision = s->hs.auto_precision;
+    info->bounds_min[0] = s->hs.bounds_lo.x; info->bounds_min[1] = s->hs.bounds_lo.y; info->bounds_min[2] = s->hs.bounds_lo.z;
+    info->bounds_max[0] = s->hs.bounds_hi.x; info->bounds_max[1] = s->hs.bounds_hi.y; info->bounds_max[2] = s->hs.bounds_hi.z;
+    info->build_ms_ref = s->ms_ref;
+    info->build_ms_fast = s->ms_fast;
+    return PATHS_OK;
+}
+
+paths_status paths_scene_prim_entity(const paths_scene *s, uint32_t prim, int32_t *is_light, uint32_t *entity, uint32_t *face) {
+    if (!s) return fail(PATHS_ERR_INVALID_ARG, "null scene");
+    if (prim >= s->hs.prims.size()) return fail(PATHS_ERR_INVALID_ARG, "prim id out of range");
+    const HostPrim &p = s->hs.prims[prim];
+    if (is_light) *is_light = p.is_light;
+    if (entity) *entity = p.entity;
+    if (face) *face = p.face;
+    return PATHS_OK;
+}
+
+paths_status paths_trace_closest(paths_scene *s, int32_t device, const double *origins, const double *dirs, size_t n, uint32_t *prim_id, double *t,
+                                 double *bary, int32_t precision) {
+    PATHS_GUARD_BEGIN
+    if (!s || (n && (!origins || !dirs || !prim_id || !t))) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    paths_status st = check_device(device);
+    if (st != PATHS_OK) return st;
+    int prec = resolve_precision(s, precision);
+    const SceneDevice *sd = nullptr;
+    st = ensure_staged(s, device, prec == 64, prec == 32, &sd);
+    if (st != PATHS_OK) return st;
+    std::string err;
+    st = prec == 64 ? trace_closest_f64(sd, origins, dirs, n, prim_id, t, bary, err) : trace_closest_f32(sd, origins, dirs, n, prim_id, t, bary, err);
+    return st == PATHS_OK ? st : fail(st, err);
+    PATHS_GUARD_END
+}
+
+void paths_render_opts_default(paths_render_opts *o) {
+    if (!o) return;
+    std::memset(o, 0, sizeof(*o));
+    o->precision = PATHS_PRECISION_AUTO;
+    o->shard_mode = PATHS_SHARD_SAMPLES;
+    o->world = 1;
+    o->seed = 1;
+    o->max_bounces = 10; // trace.rs:14
+}
+
+paths_status paths_renderer_create(paths_scene *s, const paths_camera *cam, const paths_render_opts *opts_in, paths_renderer **out) {
+    PATHS_GUARD_BEGIN
+    if (!s || !cam || !out) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    *out = nullptr;
+    paths_render_opts opts;
+    if (opts_in) opts = *opts_in;
+    else paths_render_opts_default(&opts);
+    if (cam->image_width == 0 || cam->image_height == 0 || (uint64_t)cam->image_width * cam->image_height > 0x40000000ull)
+        return fail(PATHS_ERR_INVALID_ARG, "bad image size");
+    if (opts.max_bounces > 250) return fail(PATHS_ERR_INVALID_ARG, "max_bounces > 250");
+    if (opts.shard_mode != PATHS_SHARD_SAMPLES && opts.shard_mode != PATHS_SHARD_TILES) return fail(PATHS_ERR_INVALID_ARG, "unknown shard mode");
+    paths_status st = check_device(opts.device);
+    if (st != PATHS_OK) return st;
+    int prec = resolve_precision(s, opts.precision);
+    opts.precision = prec;
+    const SceneDevice *sd = nullptr;
+    st = ensure_staged(s, opts.device, prec == 64, prec == 32, &sd);
+    if (st != PATHS_OK) return st;
+    std::string err;
+    RendererBase *impl = prec == 64 ? make_renderer_f64(sd, *cam, opts, err) : make_renderer_f32(sd, *cam, opts, err);
+    if (!impl) return fail(PATHS_ERR_CUDA, err);
+    paths_renderer *r = new paths_renderer();
+    r->impl = impl;
+    r->scene = s;
+    r->w = cam->image_width;
+    r->h = cam->image_height;
+    *out = r;
+    return PATHS_OK;
+    PATHS_GUARD_END
+}
+
+#define PATHS_FORWARD(expr)                                         \
+    PATHS_GUARD_BEGIN                                               \
+    if (!r) return fail(PATHS_ERR_INVALID_ARG, "null renderer");    \
+    paths_status st = (expr);                                       \
+    return st == PATHS_OK ? st : fail(st, r->impl->err);            \
+    PATHS_GUARD_END
+
+paths_status paths_renderer_render(paths_renderer *r, uint32_t spp) { PATHS_FORWARD(r->impl->render(spp, true)) }
+paths_status paths_renderer_render_async(paths_renderer *r, uint32_t spp) { PATHS_FORWARD(r->impl->render(spp, false)) }
+paths_status paths_renderer_sync(paths_renderer *r) { PATHS_FORWARD(r->impl->sync()) }
+paths_status paths_renderer_image_f32(paths_renderer *r, float *rgb) {
+    if (!rgb) return fail(PATHS_ERR_INVALID_ARG, "null buffer");
+    PATHS_FORWARD(r->impl->image_f32(rgb))
+}
+paths_status paths_renderer_image_rgb24(paths_renderer *r, uint8_t *rgb) {
+    if (!rgb) return fail(PATHS_ERR_INVALID_ARG, "null buffer");
+    PATHS_FORWARD(r->impl->image_rgb24(rgb))
+}
+paths_status paths_renderer_get_sums(paths_renderer *r, double *sums4) {
+    if (!sums4) return fail(PATHS_ERR_INVALID_ARG, "null buffer");
+    PATHS_FORWARD(r->impl->get_sums(sums4))
+}
+paths_status paths_renderer_add_sums(paths_renderer *r, const double *sums4) {
+    if (!sums4) return fail(PATHS_ERR_INVALID_ARG, "null buffer");
+    PATHS_FORWARD(r->impl->add_sums(sums4))
+}
+paths_status paths_renderer_device_sums(paths_renderer *r, void **device_ptr, size_t *n_elems, int32_t *elem_bytes) {
+    if (!device_ptr || !n_elems || !elem_bytes) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    PATHS_FORWARD(r->impl->device_sums(device_ptr, n_elems, elem_bytes))
+}
+paths_status paths_renderer_get_stats(paths_renderer *r, paths_stats *st_out) {
+    if (!st_out) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    PATHS_FORWARD(r->impl->get_stats(st_out))
+}
+paths_status paths_renderer_set_camera(paths_renderer *r, const double location[3], const double rot[9]) {
+    if (!location || !rot) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    PATHS_FORWARD(r->impl->set_camera(location, rot))
+}
+paths_status paths_renderer_reset(paths_renderer *r) { PATHS_FORWARD(r->impl->reset()) }
+void paths_renderer_destroy(paths_renderer *r) { delete r; }
+
+paths_status paths_camera_rays(const paths_camera *cam, int32_t device, uint64_t seed, uint32_t sample, uint32_t x0, uint32_t y0, uint32_t w,
+                               uint32_t h, double *o, double *d, double *weight, int32_t precision) {
+    PATHS_GUARD_BEGIN
+    if (!cam || !o || !d || !weight) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    if ((uint64_t)x0 + w > cam->image_width || (uint64_t)y0 + h > cam->image_height) return fail(PATHS_ERR_INVALID_ARG, "rectangle outside the image");
+    paths_status st = check_device(device);
+    if (st != PATHS_OK) return st;
+    std::string err;
+    st = precision == PATHS_PRECISION_F32 ? camera_rays_f32(*cam, device, seed, sample, x0, y0, w, h, o, d, weight, err)
+                                          : camera_rays_f64(*cam, device, seed, sample, x0, y0, w, h, o, d, weight, err);
+    return st == PATHS_OK ? st : fail(st, err);
+    PATHS_GUARD_END
+}
+
+paths_status paths_write_ppm(const char *path, const uint8_t *rgb, uint32_t w, uint32_t h) {
+    if (!path || !rgb) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    FILE *f = std::fopen(path, "wb");
+    if (!f) return fail(PATHS_ERR_IO, std::string("cannot open ") + path);
+    std::fprintf(f, "P6\n%u %u\n255\n", w, h);
+    size_t n = (size_t)w * h * 3;
+    bool ok = std::fwrite(rgb, 1, n, f) == n;
+    ok = (std::fclose(f) == 0) && ok;
+    return ok ? PATHS_OK : fail(PATHS_ERR_IO, std::string("short write to ") + path);
+}
+
+paths_status paths_write_pfm(const char *path, const float *rgb, uint32_t w, uint32_t h) {
+    if (!path || !rgb) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    FILE *f = std::fopen(path, "wb");
+    if (!f) return fail(PATHS_ERR_IO, std::string("cannot open ") + path);
+    std::fprintf(f, "PF\n%u %u\n-1.0\n", w, h);
+    bool ok = true;
+    for (uint32_t y = 0; y < h && ok; y++) // PFM stores the bottom row first
+        ok = std::fwrite(rgb + (size_t)(h - 1 - y) * w * 3, sizeof(float), (size_t)w * 3, f) == (size_t)w * 3;
+    ok = (std::fclose(f) == 0) && ok;
+    return ok ? PATHS_OK : fail(PATHS_ERR_IO, std::string("short write to ") + path);
+}
+
+} // extern "C"

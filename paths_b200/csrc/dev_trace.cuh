@@ -80,7 +80,7 @@ __device__ __forceinline__ bool slab_ref(const double *box, D3v o, D3v inv, bool
 #define PATHS_REF_STACK 100 /* src/bvh.rs:79 */
 
 // src/bvh.rs:78-140.  Returns the closest hit in the reference's visiting order (first found wins exact ties).
-__device__ __noinline__ Hit64 trace_ref(const DevScene &sc, D3v o, D3v d) {
+static __device__ __noinline__ Hit64 trace_ref(const DevScene &sc, D3v o, D3v d) {
     Hit64 best;
     best.prim = 0xFFFFFFFFu;
     best.t = 0.0;

@@ -72,7 +72,7 @@ __global__ void __launch_bounds__(128) k_extend(DevScene sc, PathState<typename 
         if (i < count) {
             uint32_t slot = queue ? queue[i] : i;
             typename Vec4T<R>::type o = ps.ray_o[slot], d = ps.ray_d[slot];
-            if (IsF64<R>::value) {
+            if constexpr (IsF64<R>::value) {
                 Hit64 h = trace_ref(sc, mk3((double)o.x, (double)o.y, (double)o.z), mk3((double)d.x, (double)d.y, (double)d.z));
                 ps.hit[slot] = mk4(bits_to_real(h.prim, R(0)), R(h.t), R(h.bx), R(h.by));
             } else {
@@ -263,7 +263,7 @@ __global__ void __launch_bounds__(128) k_shadow(DevScene sc, PathState<typename 
             R4 o = ps.sh_o[i], d = ps.sh_d[i];
             uint32_t lid = real_to_bits(o.w), slot = real_to_bits(d.w);
             bool occluded;
-            if (IsF64<R>::value) {
+            if constexpr (IsF64<R>::value) {
                 // the reference runs a full closest-hit query and compares entities (trace.rs:61-66)
                 Hit64 h = trace_ref(sc, mk3((double)o.x, (double)o.y, (double)o.z), mk3((double)d.x, (double)d.y, (double)d.z));
                 occluded = false;
@@ -318,7 +318,7 @@ __global__ void __launch_bounds__(256) k_accumulate(PathState<typename Vec4T<R>:
     }
 }
 
-__global__ void k_tally(PassControl pc, uint32_t n_bounces, uint32_t n_slots) {
+template <typename R> __global__ void k_tally(PassControl pc, uint32_t n_bounces, uint32_t n_slots) {
     if (threadIdx.x == 0 && blockIdx.x == 0) {
         unsigned long long e = 0, s = 0;
         for (uint32_t b = 0; b < n_bounces; b++) {

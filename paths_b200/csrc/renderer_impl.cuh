@@ -1,0 +1,310 @@
+// renderer_impl.cuh -- RendererImpl<R>: buffers, pass loop and estimator for one GPU (see renderer.cuh).
+#pragma once
+#include "renderer.cuh"
+
+namespace paths {
+
+template <typename R> class RendererImpl : public RendererBase {
+    typedef typename Vec4T<R>::type R4;
+
+    const SceneDevice *sd_;
+    paths_render_opts opts_;
+    DevCamera cam_;
+    cudaStream_t stream_ = nullptr;
+    uint32_t W_, H_, npix_, n_local_ = 0, spp_pass_ = 1, n_ctl_ = 0;
+    size_t n_slots_max_ = 0;
+    uint32_t samples_done_ = 0; // global samples per pixel issued so far (all ranks together)
+    int sm_count_ = 148, grid_trace_ = 0, grid_shade_ = 0, grid_stream_ = 0;
+    // device buffers
+    R4 *sums_ = nullptr;
+    uint32_t *pixels_ = nullptr; // tile shard: local -> global pixel
+    PathState<R4> ps_;
+    PassControl pc_;
+    uint32_t *ctl_block_ = nullptr;
+    std::vector<void *> allocs_;
+    // stats
+    paths_stats stats_;
+    struct Timed {
+        cudaEvent_t a, b;
+        int cls;
+    };
+    std::vector<Timed> timed_;
+    std::vector<cudaEvent_t> pool_;
+
+    template <typename T> paths_status alloc(T **p, size_t count) {
+        void *q = nullptr;
+        PATHS_CU(cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(T)));
+        allocs_.push_back(q);
+        *p = (T *)q;
+        return PATHS_OK;
+    }
+    cudaEvent_t get_event() {
+        if (!pool_.empty()) {
+            cudaEvent_t e = pool_.back();
+            pool_.pop_back();
+            return e;
+        }
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        return e;
+    }
+    void tic(int cls) {
+        if (!opts_.time_kernels) return;
+        Timed t;
+        t.a = get_event();
+        t.b = get_event();
+        t.cls = cls;
+        cudaEventRecord(t.a, stream_);
+        timed_.push_back(t);
+    }
+    void toc() {
+        stats_.kernel_launches++;
+        if (!opts_.time_kernels) return;
+        cudaEventRecord(timed_.back().b, stream_);
+    }
+    void resolve_timers() {
+        for (Timed &t : timed_) {
+            float ms = 0.0f;
+            cudaEventElapsedTime(&ms, t.a, t.b);
+            double *dst[] = {&stats_.ms_raygen, &stats_.ms_extend, &stats_.ms_shade, &stats_.ms_shadow, &stats_.ms_accumulate};
+            *dst[t.cls] += ms;
+            stats_.ms_total += ms;
+            pool_.push_back(t.a);
+            pool_.push_back(t.b);
+        }
+        timed_.clear();
+    }
+
+  public:
+    RendererImpl(const SceneDevice *sd, const paths_camera &cam, const paths_render_opts &o) : sd_(sd), opts_(o) {
+        cam_ = make_dev_camera(cam);
+        W_ = cam.image_width;
+        H_ = cam.image_height;
+        npix_ = W_ * H_;
+        std::memset(&stats_, 0, sizeof(stats_));
+        std::memset(&ps_, 0, sizeof(ps_));
+        std::memset(&pc_, 0, sizeof(pc_));
+    }
+    ~RendererImpl() override {
+        cudaSetDevice(sd_->device);
+        if (stream_) cudaStreamSynchronize(stream_);
+        for (Timed &t : timed_) {
+            cudaEventDestroy(t.a);
+            cudaEventDestroy(t.b);
+        }
+        for (cudaEvent_t e : pool_) cudaEventDestroy(e);
+        for (void *p : allocs_) cudaFree(p);
+        if (stream_) cudaStreamDestroy(stream_);
+    }
+
+    paths_status init() {
+        PATHS_CU(cudaSetDevice(sd_->device));
+        cudaDeviceProp prop;
+        PATHS_CU(cudaGetDeviceProperties(&prop, sd_->device));
+        sm_count_ = prop.multiProcessorCount;
+        PATHS_CU(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
+        uint32_t world = std::max<uint32_t>(opts_.world, 1);
+        if (opts_.rank >= world) {
+            err = "rank >= world";
+            return PATHS_ERR_INVALID_ARG;
+        }
+        // ---- shard: which pixels this rank owns
+        if (opts_.shard_mode == PATHS_SHARD_TILES && world > 1) {
+            std::vector<uint32_t> own;
+            uint32_t tiles_x = (W_ + 63) / 64;
+            for (uint32_t y = 0; y < H_; y++)
+                for (uint32_t x = 0; x < W_; x++)
+                    if (((y / 64) * tiles_x + (x / 64)) % world == opts_.rank) own.push_back(x + y * W_);
+            n_local_ = (uint32_t)own.size();
+            if (alloc(&pixels_, own.size()) != PATHS_OK) return PATHS_ERR_CUDA;
+            if (!own.empty()) PATHS_CU(cudaMemcpy(pixels_, own.data(), own.size() * 4, cudaMemcpyHostToDevice));
+        } else {
+            n_local_ = npix_;
+        }
+        // ---- wavefront size: about 8M paths in flight unless told otherwise
+        spp_pass_ = opts_.samples_per_pass;
+        if (spp_pass_ == 0) spp_pass_ = (uint32_t)std::min<uint64_t>(64, std::max<uint64_t>(1, (8u << 20) / std::max<uint32_t>(n_local_, 1)));
+        n_slots_max_ = (size_t)std::max<uint32_t>(n_local_, 1) * spp_pass_;
+        if (n_slots_max_ > 0x7FFFFFFFull) {
+            err = "samples_per_pass * pixels exceeds 2^31 slots";
+            return PATHS_ERR_INVALID_ARG;
+        }
+        if (alloc(&sums_, npix_) != PATHS_OK) return PATHS_ERR_CUDA;
+        PATHS_CU(cudaMemset(sums_, 0, (size_t)npix_ * sizeof(R4)));
+        R4 **state[] = {&ps_.ray_o, &ps_.ray_d, &ps_.hit, &ps_.thr, &ps_.col, &ps_.sh_o, &ps_.sh_d, &ps_.sh_c};
+        for (R4 **p : state)
+            if (alloc(p, n_slots_max_) != PATHS_OK) return PATHS_ERR_CUDA;
+        if (alloc(&pc_.queue[0], n_slots_max_) != PATHS_OK || alloc(&pc_.queue[1], n_slots_max_) != PATHS_OK) return PATHS_ERR_CUDA;
+        uint32_t nb = opts_.max_bounces + 2;
+        n_ctl_ = 5 * nb;
+        if (alloc(&ctl_block_, n_ctl_) != PATHS_OK) return PATHS_ERR_CUDA;
+        pc_.qcount = ctl_block_;
+        pc_.scount = ctl_block_ + nb;
+        pc_.work = ctl_block_ + 2 * nb;
+        if (alloc(&pc_.totals, 4) != PATHS_OK) return PATHS_ERR_CUDA;
+        PATHS_CU(cudaMemset(pc_.totals, 0, 4 * sizeof(unsigned long long)));
+        // ---- persistent grids: every SM full
+        int bps = 0;
+        PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_extend<R>, 128, 0));
+        grid_trace_ = sm_count_ * std::max(bps, 1);
+        PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_shade<R>, 128, 0));
+        grid_shade_ = sm_count_ * std::max(bps, 1);
+        grid_stream_ = sm_count_ * 8;
+        return PATHS_OK;
+    }
+
+    paths_status run_pass(uint32_t s_base, uint32_t n_spp) {
+        const uint32_t n_slots = n_local_ * n_spp;
+        if (n_slots == 0) return PATHS_OK;
+        const uint32_t k0 = (uint32_t)opts_.seed, k1 = (uint32_t)(opts_.seed >> 32);
+        ShardInfo shard;
+        shard.n_local = n_local_;
+        shard.pixels = pixels_;
+        const uint32_t nb = opts_.max_bounces + 1; // segments per path (trace.rs:13-16)
+        PATHS_CU(cudaMemsetAsync(ctl_block_, 0, n_ctl_ * sizeof(uint32_t), stream_));
+        tic(0);
+        k_raygen<R><<<grid_stream_, 256, 0, stream_>>>(cam_, k0, k1, shard, s_base, n_slots, ps_, pc_);
+        toc();
+        for (uint32_t b = 0; b < nb; b++) {
+            const uint32_t *q = b == 0 ? nullptr : pc_.queue[b & 1];
+            tic(1);
+            k_extend<R><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, pc_.qcount + b, pc_.work + 3 * b);
+            toc();
+            stats_.n_extend_launches++;
+            tic(2);
+            k_shade<R><<<grid_shade_, 128, 0, stream_>>>(sd_->view, ps_, shard, s_base, k0, k1, opts_.max_bounces, q, pc_.queue[(b + 1) & 1],
+                                                        pc_.qcount + b, pc_.qcount + b + 1, pc_.scount + b, pc_.work + 3 * b + 1, pc_.totals);
+            toc();
+            if (sd_->view.n_lights > 0) {
+                tic(3);
+                k_shadow<R><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
+                toc();
+                stats_.n_shadow_launches++;
+            }
+        }
+        tic(4);
+        k_accumulate<R><<<grid_stream_, 256, 0, stream_>>>(ps_, shard, n_spp, sums_);
+        toc();
+        k_tally<R><<<1, 32, 0, stream_>>>(pc_, nb, n_slots);
+        stats_.kernel_launches++;
+        stats_.passes++;
+        PATHS_CU(cudaGetLastError());
+        return PATHS_OK;
+    }
+
+    paths_status render(uint32_t spp, bool wait) override {
+        PATHS_CU(cudaSetDevice(sd_->device));
+        uint32_t world = std::max<uint32_t>(opts_.world, 1);
+        uint32_t s0 = samples_done_, s1 = samples_done_ + spp;
+        if (opts_.shard_mode == PATHS_SHARD_SAMPLES && world > 1) { // this rank's slice of the sample range
+            uint32_t lo = (uint32_t)((uint64_t)spp * opts_.rank / world), hi = (uint32_t)((uint64_t)spp * (opts_.rank + 1) / world);
+            s0 = samples_done_ + lo;
+            s1 = samples_done_ + hi;
+        }
+        for (uint32_t s = s0; s < s1; s += spp_pass_) {
+            paths_status st = run_pass(s, std::min(spp_pass_, s1 - s));
+            if (st != PATHS_OK) return st;
+        }
+        samples_done_ += spp;
+        return wait ? sync() : PATHS_OK;
+    }
+    paths_status sync() override {
+        PATHS_CU(cudaSetDevice(sd_->device));
+        PATHS_CU(cudaStreamSynchronize(stream_));
+        resolve_timers();
+        return PATHS_OK;
+    }
+    paths_status image_f32(float *rgb) override {
+        PATHS_CU(cudaSetDevice(sd_->device));
+        float *d = nullptr;
+        PATHS_CU(cudaMalloc(&d, (size_t)npix_ * 12));
+        k_image_f32<R><<<(npix_ + 255) / 256, 256, 0, stream_>>>(sums_, npix_, d);
+        cudaError_t e = cudaMemcpyAsync(rgb, d, (size_t)npix_ * 12, cudaMemcpyDeviceToHost, stream_);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(stream_);
+        cudaFree(d);
+        PATHS_CU(e);
+        return PATHS_OK;
+    }
+    paths_status image_rgb24(uint8_t *rgb) override {
+        PATHS_CU(cudaSetDevice(sd_->device));
+        uint8_t *d = nullptr;
+        PATHS_CU(cudaMalloc(&d, (size_t)npix_ * 3));
+        k_image_rgb24<R><<<(npix_ + 255) / 256, 256, 0, stream_>>>(sums_, npix_, d);
+        cudaError_t e = cudaMemcpyAsync(rgb, d, (size_t)npix_ * 3, cudaMemcpyDeviceToHost, stream_);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(stream_);
+        cudaFree(d);
+        PATHS_CU(e);
+        return PATHS_OK;
+    }
+    paths_status get_sums(double *sums4) override {
+        PATHS_CU(cudaSetDevice(sd_->device));
+        double4 *d = nullptr;
+        PATHS_CU(cudaMalloc(&d, (size_t)npix_ * 32));
+        k_sums_to_f64<R><<<(npix_ + 255) / 256, 256, 0, stream_>>>(sums_, npix_, d);
+        cudaError_t e = cudaMemcpyAsync(sums4, d, (size_t)npix_ * 32, cudaMemcpyDeviceToHost, stream_);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(stream_);
+        cudaFree(d);
+        PATHS_CU(e);
+        return PATHS_OK;
+    }
+    paths_status add_sums(const double *sums4) override {
+        PATHS_CU(cudaSetDevice(sd_->device));
+        double4 *d = nullptr;
+        PATHS_CU(cudaMalloc(&d, (size_t)npix_ * 32));
+        cudaError_t e = cudaMemcpyAsync(d, sums4, (size_t)npix_ * 32, cudaMemcpyHostToDevice, stream_);
+        if (e == cudaSuccess) {
+            k_add_sums<R><<<(npix_ + 255) / 256, 256, 0, stream_>>>(sums_, npix_, d);
+            e = cudaStreamSynchronize(stream_);
+        }
+        cudaFree(d);
+        PATHS_CU(e);
+        return PATHS_OK;
+    }
+    paths_status device_sums(void **ptr, size_t *n, int32_t *elem_bytes) override {
+        *ptr = sums_;
+        *n = (size_t)npix_ * 4;
+        *elem_bytes = (int32_t)sizeof(R);
+        return PATHS_OK;
+    }
+    paths_status get_stats(paths_stats *st) override {
+        PATHS_CU(cudaSetDevice(sd_->device));
+        PATHS_CU(cudaStreamSynchronize(stream_));
+        resolve_timers();
+        unsigned long long t[4];
+        PATHS_CU(cudaMemcpy(t, pc_.totals, sizeof(t), cudaMemcpyDeviceToHost));
+        stats_.extend_rays = t[0];
+        stats_.shadow_rays = t[1];
+        stats_.bad_samples = t[2];
+        stats_.samples = t[3];
+        *st = stats_;
+        return PATHS_OK;
+    }
+    paths_status set_camera(const double loc[3], const double rot[9]) override { // renderer.rs:112-120
+        for (int i = 0; i < 3; i++) cam_.location[i] = loc[i];
+        for (int i = 0; i < 9; i++) cam_.rot[i] = rot[i];
+        return reset();
+    }
+    paths_status reset() override { // renderer.rs:122-128,143-150: a new epoch drops the estimator
+        PATHS_CU(cudaSetDevice(sd_->device));
+        PATHS_CU(cudaStreamSynchronize(stream_));
+        PATHS_CU(cudaMemset(sums_, 0, (size_t)npix_ * sizeof(R4)));
+        PATHS_CU(cudaMemset(pc_.totals, 0, 4 * sizeof(unsigned long long)));
+        samples_done_ = 0;
+        resolve_timers();
+        std::memset(&stats_, 0, sizeof(stats_));
+        return PATHS_OK;
+    }
+};
+
+template <typename R>
+RendererBase *make_renderer_impl(const SceneDevice *sd, const paths_camera &cam, const paths_render_opts &opts, std::string &err) {
+    RendererImpl<R> *r = new RendererImpl<R>(sd, cam, opts);
+    if (r->init() != PATHS_OK) {
+        err = r->err;
+        delete r;
+        return nullptr;
+    }
+    return r;
+}
+
+} // namespace paths

@@ -1,0 +1,51 @@
+// scene_device.h -- a scene staged into one GPU's HBM (read-only, shared by every renderer on that device).
+#pragma once
+#include <string>
+#include <vector>
+
+#include "dev_scene.h"
+#include "host_scene.h"
+
+namespace paths {
+
+struct SceneDevice {
+    int device = -1;
+    DevScene view;
+    std::vector<void *> allocs;
+    size_t bytes = 0;
+    ~SceneDevice();
+};
+
+// Uploads the scene; ref / fast may be null (the matching kernels then must not be used).
+SceneDevice *upload_scene(int device, const HostScene &hs, const RefTree *ref, const FastTree *fast, std::string &err);
+
+struct RendererBase {
+    virtual ~RendererBase() {}
+    virtual paths_status render(uint32_t spp, bool wait) = 0;
+    virtual paths_status sync() = 0;
+    virtual paths_status image_f32(float *rgb) = 0;
+    virtual paths_status image_rgb24(uint8_t *rgb) = 0;
+    virtual paths_status get_sums(double *sums4) = 0;
+    virtual paths_status add_sums(const double *sums4) = 0;
+    virtual paths_status device_sums(void **ptr, size_t *n, int32_t *elem_bytes) = 0;
+    virtual paths_status get_stats(paths_stats *st) = 0;
+    virtual paths_status set_camera(const double loc[3], const double rot[9]) = 0;
+    virtual paths_status reset() = 0;
+    std::string err;
+};
+
+DevCamera make_dev_camera(const paths_camera &c); // CameraDescription::to_camera (src/serde.rs:172-188)
+
+// one factory + two batch entry points per arithmetic type, instantiated in kernels_f32.cu / kernels_f64.cu
+RendererBase *make_renderer_f32(const SceneDevice *sd, const paths_camera &cam, const paths_render_opts &opts, std::string &err);
+RendererBase *make_renderer_f64(const SceneDevice *sd, const paths_camera &cam, const paths_render_opts &opts, std::string &err);
+paths_status trace_closest_f32(const SceneDevice *sd, const double *o, const double *d, size_t n, uint32_t *prim, double *t, double *bary,
+                               std::string &err);
+paths_status trace_closest_f64(const SceneDevice *sd, const double *o, const double *d, size_t n, uint32_t *prim, double *t, double *bary,
+                               std::string &err);
+paths_status camera_rays_f32(const paths_camera &cam, int device, uint64_t seed, uint32_t sample, uint32_t x0, uint32_t y0, uint32_t w, uint32_t h,
+                             double *o, double *d, double *weight, std::string &err);
+paths_status camera_rays_f64(const paths_camera &cam, int device, uint64_t seed, uint32_t sample, uint32_t x0, uint32_t y0, uint32_t w, uint32_t h,
+                             double *o, double *d, double *weight, std::string &err);
+
+} // namespace paths
