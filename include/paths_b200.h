@@ -145,6 +145,7 @@ typedef struct {
     uint64_t passes;
     double ms_raygen, ms_extend, ms_shade, ms_shadow, ms_accumulate, ms_total; /* valid with time_kernels */
     uint64_t n_extend_launches, n_shadow_launches;
+    double ms_device; /* device time of all render calls since reset: CUDA events on the launching stream, first to last kernel */
 } paths_stats;
 
 typedef struct {
@@ -206,6 +207,9 @@ paths_status paths_renderer_get_sums(paths_renderer *r, double *sums4 /* W*H*4 *
 paths_status paths_renderer_add_sums(paths_renderer *r, const double *sums4);
 /* device-resident estimator buffer for in-place collectives (NCCL reduce over NVLink): W*H*4 elements of f32 (elem_bytes 4) or f64 (8) */
 paths_status paths_renderer_device_sums(paths_renderer *r, void **device_ptr, size_t *n_elems, int32_t *elem_bytes);
+/* the CUDA stream (cudaStream_t) every kernel of this renderer is launched on, so a caller can order collectives and
+ * CUDA events against the render without a host synchronisation */
+paths_status paths_renderer_cuda_stream(paths_renderer *r, void **stream);
 /* num_rays_cast (renderer.rs:75-77) and friends */
 paths_status paths_renderer_get_stats(paths_renderer *r, paths_stats *st);
 /* set_camera(location, orientation) (renderer.rs:112-120): new epoch; rot is row-major 3x3 */

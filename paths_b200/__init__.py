@@ -249,6 +249,12 @@ class Renderer:
         check(lib().paths_renderer_device_sums(self._h, C.byref(ptr), C.byref(n), C.byref(eb)))
         return ptr.value, n.value, eb.value
 
+    def cuda_stream(self):
+        """cudaStream_t (as an int) all kernels of this renderer run on."""
+        s = C.c_void_p()
+        check(lib().paths_renderer_cuda_stream(self._h, C.byref(s)))
+        return s.value or 0
+
     def set_camera(self, location, orientation):
         """renderer.rs:112-120: orientation is a row-major 3x3 rotation; starts a new epoch."""
         loc = np.ascontiguousarray(location, dtype=np.float64)

@@ -78,7 +78,8 @@ class Stats(C.Structure):
     _fields_ = [("samples", C.c_uint64), ("extend_rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("bad_samples", C.c_uint64),
                 ("kernel_launches", C.c_uint64), ("passes", C.c_uint64), ("ms_raygen", C.c_double), ("ms_extend", C.c_double),
                 ("ms_shade", C.c_double), ("ms_shadow", C.c_double), ("ms_accumulate", C.c_double), ("ms_total", C.c_double),
-                ("n_extend_launches", C.c_uint64), ("n_shadow_launches", C.c_uint64)]
+                ("n_extend_launches", C.c_uint64), ("n_shadow_launches", C.c_uint64),
+                ("ms_device", C.c_double)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -121,6 +122,7 @@ SIGNATURES = {
     "paths_renderer_get_sums": (C.c_int, [VP, VP]),
     "paths_renderer_add_sums": (C.c_int, [VP, VP]),
     "paths_renderer_device_sums": (C.c_int, [VP, C.POINTER(VP), C.POINTER(C.c_size_t), C.POINTER(C.c_int32)]),
+    "paths_renderer_cuda_stream": (C.c_int, [VP, C.POINTER(VP)]),
     "paths_renderer_get_stats": (C.c_int, [VP, C.POINTER(Stats)]),
     "paths_renderer_set_camera": (C.c_int, [VP, VP, VP]),
     "paths_renderer_reset": (C.c_int, [VP]),

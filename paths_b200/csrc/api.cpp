@@ -311,6 +311,10 @@ paths_status paths_renderer_device_sums(paths_renderer *r, void **device_ptr, si
     if (!device_ptr || !n_elems || !elem_bytes) return fail(PATHS_ERR_INVALID_ARG, "null argument");
     PATHS_FORWARD(r->impl->device_sums(device_ptr, n_elems, elem_bytes))
 }
+paths_status paths_renderer_cuda_stream(paths_renderer *r, void **stream) {
+    if (!stream) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    PATHS_FORWARD(r->impl->cuda_stream(stream))
+}
 paths_status paths_renderer_get_stats(paths_renderer *r, paths_stats *st_out) {
     if (!st_out) return fail(PATHS_ERR_INVALID_ARG, "null argument");
     PATHS_FORWARD(r->impl->get_stats(st_out))

@@ -29,6 +29,7 @@ template <typename R> class RendererImpl : public RendererBase {
         int cls;
     };
     std::vector<Timed> timed_;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> spans_; // one per render() call
     std::vector<cudaEvent_t> pool_;
 
     template <typename T> paths_status alloc(T **p, size_t count) {
@@ -73,6 +74,14 @@ template <typename R> class RendererImpl : public RendererBase {
             pool_.push_back(t.b);
         }
         timed_.clear();
+        for (auto &sp : spans_) {
+            float ms = 0.0f;
+            cudaEventElapsedTime(&ms, sp.first, sp.second);
+            stats_.ms_device += ms;
+            pool_.push_back(sp.first);
+            pool_.push_back(sp.second);
+        }
+        spans_.clear();
     }
 
   public:
@@ -91,6 +100,10 @@ template <typename R> class RendererImpl : public RendererBase {
         for (Timed &t : timed_) {
             cudaEventDestroy(t.a);
             cudaEventDestroy(t.b);
+        }
+        for (auto &sp : spans_) {
+            cudaEventDestroy(sp.first);
+            cudaEventDestroy(sp.second);
         }
         for (cudaEvent_t e : pool_) cudaEventDestroy(e);
         for (void *p : allocs_) cudaFree(p);
@@ -201,10 +214,14 @@ template <typename R> class RendererImpl : public RendererBase {
             s0 = samples_done_ + lo;
             s1 = samples_done_ + hi;
         }
+        cudaEvent_t ea = get_event(), eb = get_event();
+        cudaEventRecord(ea, stream_);
         for (uint32_t s = s0; s < s1; s += spp_pass_) {
             paths_status st = run_pass(s, std::min(spp_pass_, s1 - s));
             if (st != PATHS_OK) return st;
         }
+        cudaEventRecord(eb, stream_);
+        spans_.push_back(std::make_pair(ea, eb));
         samples_done_ += spp;
         return wait ? sync() : PATHS_OK;
     }
@@ -264,6 +281,10 @@ template <typename R> class RendererImpl : public RendererBase {
         *ptr = sums_;
         *n = (size_t)npix_ * 4;
         *elem_bytes = (int32_t)sizeof(R);
+        return PATHS_OK;
+    }
+    paths_status cuda_stream(void **stream) override {
+        *stream = (void *)stream_;
         return PATHS_OK;
     }
     paths_status get_stats(paths_stats *st) override {

@@ -28,6 +28,7 @@ struct RendererBase {
     virtual paths_status get_sums(double *sums4) = 0;
     virtual paths_status add_sums(const double *sums4) = 0;
     virtual paths_status device_sums(void **ptr, size_t *n, int32_t *elem_bytes) = 0;
+    virtual paths_status cuda_stream(void **stream) = 0;
     virtual paths_status get_stats(paths_stats *st) = 0;
     virtual paths_status set_camera(const double loc[3], const double rot[9]) = 0;
     virtual paths_status reset() = 0;
