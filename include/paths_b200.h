@@ -178,6 +178,9 @@ void paths_scene_destroy(paths_scene *s);
 paths_status paths_scene_build_bvh(paths_scene *s, int32_t which);
 paths_status paths_scene_get_info(const paths_scene *s, paths_scene_info *info);
 /* per-prim identity as the reference reports it: (is_light, entity id, face index) (bvh.rs T6, geom.rs:48-57) */
+/* flattened geometry of one item after Mesh::primitives / TrianglePrimitive::transform (src/geom.rs:111-117,251-261):
+ * triangle: a, b, c, n (12 doubles); sphere: centre, radius, then zeros.  *is_triangle may be NULL. */
+paths_status paths_scene_prim_geometry(const paths_scene *s, uint32_t prim, double out[12], int32_t *is_triangle);
 paths_status paths_scene_prim_entity(const paths_scene *s, uint32_t prim, int32_t *is_light, uint32_t *entity, uint32_t *face);
 
 /* BVH::find_intersection over a batch of host rays (src/bvh.rs:78-140).  prim_id = PATHS_MISS and t = +inf on a miss.

@@ -168,6 +168,13 @@ class Scene:
         check(lib().paths_scene_prim_entity(self._h, int(prim), C.byref(il), C.byref(en), C.byref(fa)))
         return bool(il.value), en.value, fa.value
 
+    def prim_geometry(self, prim):
+        """(is_triangle, 12 doubles): a, b, c, n of a triangle or centre, radius of a sphere, after instancing."""
+        out = np.zeros(12)
+        tri = C.c_int32()
+        check(lib().paths_scene_prim_geometry(self._h, int(prim), _p(out), C.byref(tri)))
+        return bool(tri.value), out
+
     def find_intersection(self, origins, dirs, precision=PRECISION_F64, device=0, want_bary=False):
         """BVH::find_intersection (src/bvh.rs:78-140) over a batch of rays -> (prim_id, t[, bary])."""
         o = np.ascontiguousarray(origins, dtype=np.float64).reshape(-1, 3)

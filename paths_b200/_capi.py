@@ -110,6 +110,7 @@ SIGNATURES = {
     "paths_scene_destroy": (None, [VP]),
     "paths_scene_build_bvh": (C.c_int, [VP, C.c_int32]),
     "paths_scene_get_info": (C.c_int, [VP, C.POINTER(SceneInfo)]),
+    "paths_scene_prim_geometry": (C.c_int, [VP, C.c_uint32, VP, C.POINTER(C.c_int32)]),
     "paths_scene_prim_entity": (C.c_int, [VP, C.c_uint32, C.POINTER(C.c_int32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
     "paths_trace_closest": (C.c_int, [VP, C.c_int32, VP, VP, C.c_size_t, VP, VP, VP, C.c_int32]),
     "paths_render_opts_default": (None, [C.POINTER(RenderOpts)]),

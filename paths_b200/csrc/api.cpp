@@ -224,6 +224,25 @@ paths_status paths_scene_prim_entity(const paths_scene *s, uint32_t prim, int32_
     return PATHS_OK;
 }
 
+paths_status paths_scene_prim_geometry(const paths_scene *s, uint32_t prim, double out[12], int32_t *is_triangle) {
+    if (!s || !out) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    if (prim >= s->hs.prims.size()) return fail(PATHS_ERR_INVALID_ARG, "prim id out of range");
+    const HostPrim &p = s->hs.prims[prim];
+    for (int i = 0; i < 12; i++) out[i] = 0.0;
+    if (p.type == 1) {
+        const D3 *v[4] = {&p.a, &p.b, &p.c, &p.n};
+        for (int k = 0; k < 4; k++) {
+            out[3 * k] = v[k]->x;
+            out[3 * k + 1] = v[k]->y;
+            out[3 * k + 2] = v[k]->z;
+        }
+    } else {
+        out[0] = p.a.x; out[1] = p.a.y; out[2] = p.a.z; out[3] = p.b.x;
+    }
+    if (is_triangle) *is_triangle = p.type == 1;
+    return PATHS_OK;
+}
+
 paths_status paths_trace_closest(paths_scene *s, int32_t device, const double *origins, const double *dirs, size_t n, uint32_t *prim_id, double *t,
                                  double *bary, int32_t precision) {
     PATHS_GUARD_BEGIN

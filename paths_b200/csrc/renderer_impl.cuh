@@ -1,5 +1,7 @@
 // renderer_impl.cuh -- RendererImpl<R>: buffers, pass loop and estimator for one GPU (see renderer.cuh).
 #pragma once
+#include <cstdlib>
+
 #include "renderer.cuh"
 
 namespace paths {
@@ -14,7 +16,7 @@ template <typename R> class RendererImpl : public RendererBase {
     uint32_t W_, H_, npix_, n_local_ = 0, spp_pass_ = 1, n_ctl_ = 0;
     size_t n_slots_max_ = 0;
     uint32_t samples_done_ = 0; // global samples per pixel issued so far (all ranks together)
-    int sm_count_ = 148, grid_trace_ = 0, grid_shade_ = 0, grid_stream_ = 0;
+    int sm_count_ = 148, grid_trace_ = 0, grid_shade_ = 0, grid_stream_ = 0, variant_ = 1;
     // device buffers
     R4 *sums_ = nullptr;
     uint32_t *pixels_ = nullptr; // tile shard: local -> global pixel
@@ -156,6 +158,7 @@ template <typename R> class RendererImpl : public RendererBase {
         pc_.work = ctl_block_ + 2 * nb;
         if (alloc(&pc_.totals, 4) != PATHS_OK) return PATHS_ERR_CUDA;
         PATHS_CU(cudaMemset(pc_.totals, 0, 4 * sizeof(unsigned long long)));
+        if (const char *v = getenv("PATHS_EXTEND_VARIANT")) variant_ = atoi(v); // development switch between traversal kernels
         // ---- persistent grids: every SM full
         int bps = 0;
         PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_extend<R>, 128, 0));
@@ -164,6 +167,31 @@ template <typename R> class RendererImpl : public RendererBase {
         grid_shade_ = sm_count_ * std::max(bps, 1);
         grid_stream_ = sm_count_ * 8;
         return PATHS_OK;
+    }
+
+    void launch_extend(const uint32_t *q, uint32_t b) {
+        if constexpr (!IsF64<R>::value) {
+            const uint32_t *cnt = pc_.qcount + b;
+            uint32_t *cur = pc_.work + 3 * b;
+            switch (variant_) {
+            case 1: k_extend_refill<4, 8><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 2: k_extend_refill<8, 8><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 3: k_extend_refill<4, 16><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 4: k_extend_refill<2, 4><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 5: k_extend_refill<1, 1><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
+            default: break;
+            }
+        }
+        k_extend<R><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, pc_.qcount + b, pc_.work + 3 * b);
+    }
+    void launch_shadow(uint32_t b) {
+        if constexpr (!IsF64<R>::value) {
+            if (variant_ != 0) {
+                k_shadow_refill<4, 8><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
+                return;
+            }
+        }
+        k_shadow<R><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
     }
 
     paths_status run_pass(uint32_t s_base, uint32_t n_spp) {
@@ -181,7 +209,7 @@ template <typename R> class RendererImpl : public RendererBase {
         for (uint32_t b = 0; b < nb; b++) {
             const uint32_t *q = b == 0 ? nullptr : pc_.queue[b & 1];
             tic(1);
-            k_extend<R><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, pc_.qcount + b, pc_.work + 3 * b);
+            launch_extend(q, b);
             toc();
             stats_.n_extend_launches++;
             tic(2);
@@ -190,7 +218,7 @@ template <typename R> class RendererImpl : public RendererBase {
             toc();
             if (sd_->view.n_lights > 0) {
                 tic(3);
-                k_shadow<R><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
+                launch_shadow(b);
                 toc();
                 stats_.n_shadow_launches++;
             }

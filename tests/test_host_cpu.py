@@ -1,0 +1,264 @@
+"""CPU-side tests of the product (no GPU needed): the C-ABI library loads and exports every symbol include/paths_b200.h
+declares, the C++ scene readers agree with the oracle's Python restatement of the same file formats, the host-side scene
+flattening and the reference-order AAC tree agree with the oracle, and compute entry points fail loudly without a device."""
+import ctypes as C
+import re
+import struct
+import subprocess
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+@pytest.fixture(scope="module")
+def pb():
+    import paths_b200
+
+    paths_b200.build()
+    return paths_b200
+
+
+def test_library_exports_every_declared_symbol(pb):
+    header = (ROOT / "include" / "paths_b200.h").read_text()
+    declared = set(re.findall(r"\b(paths_[a-z0-9_]+)\s*\(", header))
+    declared -= {"paths_status"}
+    assert len(declared) >= 25
+    out = subprocess.check_output(["nm", "-D", "--defined-only", str(pb._capi.LIB_PATH)], text=True)
+    exported = set(re.findall(r"\bT (paths_[a-z0-9_]+)", out))
+    assert declared <= exported, f"missing from the .so: {sorted(declared - exported)}"
+    assert declared == set(pb._capi.SIGNATURES), f"ctypes table out of date: {sorted(declared ^ set(pb._capi.SIGNATURES))}"
+    lib = pb.lib()
+    for name in declared:
+        assert getattr(lib, name) is not None
+    assert b"sm_100a" in lib.paths_version()
+
+
+def test_struct_layouts_match_the_header(pb):
+    # sizes the C compiler gives the header's structs == sizes of the ctypes mirrors
+    src = '#include <stdio.h>\n#include "paths_b200.h"\nint main(){printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu\\n",' \
+          "sizeof(paths_model_desc),sizeof(paths_material_desc),sizeof(paths_object_desc),sizeof(paths_light_desc),sizeof(paths_sky_desc)," \
+          "sizeof(paths_scene_desc),sizeof(paths_camera),sizeof(paths_render_opts),sizeof(paths_stats));return 0;}"
+    exe = ROOT / "paths_b200" / "build" / "sizes_probe"
+    exe.parent.mkdir(exist_ok=True)
+    (exe.parent / "sizes_probe.c").write_text(src)
+    subprocess.check_call(["gcc", "-I", str(ROOT / "include"), "-o", str(exe), str(exe.parent / "sizes_probe.c")])
+    got = [int(x) for x in subprocess.check_output([str(exe)], text=True).split()]
+    c = pb._capi
+    exp = [C.sizeof(t) for t in (c.ModelDesc, c.MaterialDesc, c.ObjectDesc, c.LightDesc, c.SkyDesc, c.SceneDesc, c.Camera, c.RenderOpts, c.Stats)]
+    assert got == exp
+
+
+def test_compute_fails_loudly_without_a_device(pb):
+    if pb.device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    sc = pb.Scene.load("scenes/spheres_on_plane.yml")
+    with pytest.raises(pb.PathsError) as e:
+        sc.find_intersection(np.zeros((1, 3)), np.array([[0.0, 0.0, 1.0]]))
+    assert e.value.status == pb._capi.ERR_CUDA and "no CPU path" in str(e.value)
+    with pytest.raises(pb.PathsError):
+        pb.Renderer(sc.camera, sc)
+    with pytest.raises(pb.PathsError):
+        pb.camera_rays(sc.camera, 1, 0)
+
+
+@pytest.mark.parametrize("name", ["teapot", "bunny", "spheres_on_plane", "bokeh_demo"])
+def test_yaml_loader_matches_oracle_reader(pb, oracle_mod, name):
+    # src/serde.rs schema + src/obj.rs: same camera, same flattened items (bit-equal geometry), same entity ids
+    osc, cam = oracle_mod.load_scene(f"scenes/{name}.yml")
+    gsc = pb.Scene.load(f"scenes/{name}.yml")
+    assert gsc.camera.as_dict() == cam
+    info = gsc.info
+    assert info["n_prims"] == osc.num_prims
+    step = max(1, osc.num_prims // 400)
+    for prim in list(range(0, osc.num_prims, step)) + [osc.num_prims - 1]:
+        pi = osc.prim_info(prim)
+        tri, g = gsc.prim_geometry(prim)
+        assert tri == (pi.type == 1)
+        if tri:
+            assert list(g[:9]) == list(pi.v) and list(g[9:12]) == list(pi.normal)
+        else:
+            assert list(g[:4]) == list(pi.v)[:4]
+        assert gsc.prim_entity(prim) == (bool(pi.is_light), pi.entity, pi.face)
+
+
+@pytest.mark.parametrize("name", ["teapot", "bunny", "spheres_on_plane", "bokeh_demo"])
+def test_reference_tree_matches_oracle(pb, oracle_mod, name):
+    # src/bvh.rs:160-343 restated twice (oracle and product): 2N-1 nodes and the same depth
+    osc, _ = oracle_mod.load_scene(f"scenes/{name}.yml")
+    info = pb.Scene.load(f"scenes/{name}.yml").build_bvh(reference=True)
+    assert info["ref_nodes"] == osc.num_nodes == 2 * osc.num_prims - 1
+    assert info["ref_depth"] == osc.bvh_depth
+
+
+def _soup_desc(rng, n_tris, n_spheres, with_light=True, flat=0):
+    v = rng.uniform(-3, 3, size=(n_tris, 1, 3)) + rng.normal(scale=0.3, size=(n_tris, 3, 3))
+    v = v.astype(np.float32).astype(np.float64).reshape(-1, 3)
+    if flat:  # axis-aligned triangles: invisible in the reference (flat leaf box, bvh.rs:16)
+        v[: 3 * flat, 2] = 1.5
+    faces = np.arange(3 * n_tris, dtype=np.uint32).reshape(-1, 3)
+    objects = [{"shape": "Mesh", "model": 0, "smooth_normals": True, "translation": [0.1, -0.2, 0.3], "rotation": (0.0, 0.0, 0.0) if flat else (0.3, -0.4, 0.2), "scale": 1.5,
+                "material": {"type": "Gloss", "albedo": {"type": "Rgb", "rgb": [0.8, 0.4, 0.3]}, "reflectance": 0.3, "metalness": 0.2}}]
+    for _ in range(n_spheres):
+        objects.append({"shape": "Sphere", "center": list(rng.uniform(-4, 4, 3)), "radius": float(rng.uniform(0.2, 1.0)),
+                        "material": {"type": "Lambertian", "albedo": {"type": "Rgb", "rgb": [0.5, 0.6, 0.7]}}})
+    lights = [{"geometry": "Sphere", "v": [0.0, 8.0, 0.0], "radius": 1.0, "colour": [1.0, 0.9, 0.8], "intensity": 50.0}] if with_light else []
+    return {"camera": None, "models": [{"vertices": v, "faces": faces, "vertex_colours": None, "material": None}], "objects": objects,
+            "lights": lights, "sky": {"type": "Gradient", "c0": [0.5, 0.7, 0.9], "c1": [0.8, 0.8, 0.8]}}
+
+
+@pytest.mark.parametrize("n_tris,n_spheres", [(1, 0), (7, 2), (9, 1), (10, 0), (11, 3), (100, 5), (1500, 20)])
+def test_reference_tree_on_random_soups(pb, oracle_mod, n_tris, n_spheres):
+    desc = _soup_desc(np.random.default_rng(n_tris), n_tris, n_spheres, flat=min(2, n_tris))
+    osc = oracle_mod.Scene(desc)
+    gsc = pb.Scene(desc)
+    info = gsc.build_bvh(reference=True)
+    assert info["n_prims"] == osc.num_prims and info["ref_nodes"] == osc.num_nodes and info["ref_depth"] == osc.bvh_depth
+    assert info["hidden_prims"] == min(2, n_tris)
+    fast = gsc.build_bvh(reference=False)
+    assert fast["fast_nodes"] >= 1 and fast["fast_depth"] <= 64
+
+
+def test_yaml_subset_features_and_errors(pb, oracle_mod, tmp_path):
+    # flow + block collections, quotes, comments, Fresnel / CookTorrance / Auto materials, point light, PLY with colours, OBJ with
+    # groups / quads / negative indices / MTL, HDRI sky: product reader == oracle reader
+    (tmp_path / "m.mtl").write_text("newmtl red\nKd 0.9 0.1 0.2\nnewmtl blue\nKd 0.1 0.2 0.9\n")
+    (tmp_path / "m.obj").write_text(
+        "mtllib m.mtl\nv 0 0 0\nv 1 0 0.1\nv 1 1 0.2\nv 0 1 0.3\nv 0.5 0.5 1\no first\nusemtl red\nf 1 2 3 4\ng second\nusemtl blue\n"
+        "f -1/1/1 1//1 2\nf 5 2 3\n# comment\n")
+    verts = np.array([[0, 0, 2], [1, 0, 2.5], [0, 1, 3], [1, 1, 2.2]], dtype=np.float32)
+    cols = np.array([[255, 0, 0], [0, 255, 0], [0, 0, 255], [128, 128, 128]], dtype=np.uint8)
+    with open(tmp_path / "b.ply", "wb") as fh:
+        fh.write(b"ply\nformat binary_little_endian 1.0\nelement vertex 4\nproperty float x\nproperty float y\nproperty float z\n"
+                 b"property uchar red\nproperty uchar green\nproperty uchar blue\nelement face 2\nproperty list uchar int vertex_indices\nend_header\n")
+        for v, c in zip(verts, cols):
+            fh.write(struct.pack("<fffBBB", *v, *c))
+        fh.write(struct.pack("<Biii", 3, 0, 1, 2) + struct.pack("<Biii", 3, 1, 3, 2))
+    (tmp_path / "a.ply").write_text("ply\nformat ascii 1.0\nelement vertex 3\nproperty float x\nproperty float y\nproperty float z\n"
+                                    "element face 1\nproperty list uchar int vertex_index\nend_header\n0 0 5\n1 0 5.5\n0 1 6\n3 0 1 2\n")
+    tex = np.random.default_rng(0).uniform(0.0, 4.0, size=(8, 16, 3)).astype(np.float32)
+    oracle_mod.scene_io.write_hdr(str(tmp_path / "sky.hdr"), tex)
+    yml = f"""
+# a comment
+camera:
+  image_width: 64
+  image_height: 48
+  location: {{ x: 0.0, y: 1.0, z: -6.0 }}   # trailing comment
+  orientation: {{pitch: 0.1, yaw: -0.2, roll: 0.0}}
+  sensor_width: 0.036
+  sensor_height: 0.024
+  focal_length: 0.05
+  focus_distance: 6.0
+  aperture: 4.0
+skybox:
+  type: Hdri
+  filename: "{tmp_path}/sky.hdr"
+models:
+  mesh: {{ file: '{tmp_path}/m.obj' }}
+  cloud:
+    file: {tmp_path}/b.ply
+  tri:
+    file: {tmp_path}/a.ply
+lights:
+  - colour: {{ r: 1.0, g: 1.0, b: 1.0 }}
+    intensity: 2.0
+    geometry: {{ type: Point, x: 0.0, y: -1.0, z: 0.0 }}
+  - colour: {{ r: 1.0, g: 0.5, b: 0.25 }}
+    intensity: 30.0
+    geometry:
+      type: Sphere
+      center: {{ x: 0.0, y: 6.0, z: 0.0 }}
+      radius: 0.5
+objects:
+  - shape: {{ type: Mesh, model: mesh, translation: {{x: 0.0, y: 0.0, z: 0.0}}, rotation: {{pitch: 0.0, yaw: 0.5, roll: 0.0}}, scale: 2.0 }}
+    material: {{ type: Auto }}
+  - shape:
+      type: Mesh
+      model: cloud
+      smooth_normals: false
+      translation: {{ x: 1.0, y: 0.0, z: 0.0 }}
+      rotation: {{ pitch: 0.0, yaw: 0.0, roll: 0.0 }}
+      scale: 1.0
+    material:
+      type: Lambertian
+      albedo: {{ type: Vertex }}
+  - shape: {{ type: Mesh, model: tri, translation: {{x: 0.0, y: 0.0, z: 0.0}}, rotation: {{pitch: 0.0, yaw: 0.0, roll: 0.0}}, scale: 1.0 }}
+    material:
+      type: Fresnel
+      refractive_index: 1.5
+      diffuse: {{ type: Lambertian, albedo: {{ type: Rgb, r: 0.5, g: 0.5, b: 0.5 }} }}
+      specular: {{ type: CookTorrance, albedo: {{ r: 1.0, g: 1.0, b: 1.0 }}, roughness: 0.3 }}
+  - shape: {{ type: Sphere, center: {{x: 0.0, y: -100.0, z: 0.0}}, radius: 100.0 }}
+    material: {{ type: Mirror }}
+"""
+    p = tmp_path / "scene.yml"
+    p.write_text(yml)
+    osc, cam = oracle_mod.load_scene(str(p))
+    gsc = pb.Scene.load(str(p))
+    assert gsc.camera.as_dict() == cam
+    info = gsc.info
+    assert info["n_prims"] == osc.num_prims == 2 + 2 + 2 + 1 + 1 + 1 and info["n_objects"] == 5 and info["n_lights"] == 2
+    for prim in range(osc.num_prims):
+        pi = osc.prim_info(prim)
+        tri, g = gsc.prim_geometry(prim)
+        assert list(g[:9]) == list(pi.v) if tri else list(g[:4]) == list(pi.v)[:4]
+        assert gsc.prim_entity(prim) == (bool(pi.is_light), pi.entity, pi.face)
+    # ---- errors the reference reports by panicking: here a status + message
+    bad = tmp_path / "bad.yml"
+    bad.write_text(yml.replace("  focal_length: 0.05\n", ""))
+    with pytest.raises(pb.PathsError) as e:
+        pb.Scene.load(str(bad))
+    assert e.value.status == pb._capi.ERR_PARSE and "focal_length" in str(e.value)
+    bad.write_text(yml.replace("model: tri", "model: nope"))
+    with pytest.raises(pb.PathsError) as e:
+        pb.Scene.load(str(bad))
+    assert "before declaration" in str(e.value)
+    bad.write_text(yml.replace("a.ply", "a.stl"))
+    with pytest.raises(pb.PathsError) as e:
+        pb.Scene.load(str(bad))
+    assert e.value.status in (pb._capi.ERR_UNSUPPORTED, pb._capi.ERR_IO)
+    with pytest.raises(pb.PathsError) as e:
+        pb.Scene.load(str(tmp_path / "missing.yml"))
+    assert e.value.status == pb._capi.ERR_IO
+    with pytest.raises(pb.PathsError):
+        pb.Scene({"models": [], "objects": [], "lights": [], "sky": {"type": "Flat", "c0": [0, 0, 0], "c1": [0, 0, 0]}})  # bvh.rs:201
+
+
+def test_hdr_rle_roundtrip(pb, oracle_mod, tmp_path):
+    # new-style RLE scanlines (width >= 8) decode like the flat encoding
+    rng = np.random.default_rng(3)
+    rgbe = rng.integers(1, 255, size=(4, 32, 4), dtype=np.uint8)
+    rgbe[:, 8:20] = rgbe[:, 8:9]  # runs
+    hdr = b"#?RADIANCE\nFORMAT=32-bit_rle_rgbe\n\n-Y 4 +X 32\n"
+    body = b""
+    for y in range(4):
+        body += bytes([2, 2, 0, 32])
+        for c in range(4):
+            row = rgbe[y, :, c]
+            x = 0
+            while x < 32:
+                run = 1
+                while x + run < 32 and run < 127 and row[x + run] == row[x]:
+                    run += 1
+                if run >= 3:
+                    body += bytes([128 + run, int(row[x])])
+                    x += run
+                else:
+                    lit = 1
+                    while x + lit < 32 and lit < 128 and not (x + lit + 2 < 32 and row[x + lit] == row[x + lit + 1] == row[x + lit + 2]):
+                        lit += 1
+                    body += bytes([lit]) + bytes(int(v) for v in row[x:x + lit])
+                    x += lit
+    (tmp_path / "rle.hdr").write_bytes(hdr + body)
+    (tmp_path / "flat.hdr").write_bytes(hdr + rgbe.tobytes())
+    w0, h0, t0 = oracle_mod.scene_io.load_hdr(str(tmp_path / "flat.hdr"))
+    w1, h1, t1 = oracle_mod.scene_io.load_hdr(str(tmp_path / "rle.hdr"))
+    assert (w0, h0) == (w1, h1) == (32, 4) and np.array_equal(t0, t1)
+    # the product reader is exercised through a scene whose sky is that file: both encodings must load
+    for f in ("flat.hdr", "rle.hdr"):
+        y = tmp_path / (f + ".yml")
+        y.write_text((ROOT / "scenes" / "spheres_on_plane.yml").read_text().split("skybox:")[0] + f"skybox:\n  type: Hdri\n  filename: {tmp_path}/{f}\n"
+                     + "objects:" + (ROOT / "scenes" / "spheres_on_plane.yml").read_text().split("objects:")[1])
+        assert pb.Scene.load(str(y)).info["n_prims"] == 4
