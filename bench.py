@@ -31,7 +31,19 @@ SCENES = {
     "bunny": ("scenes/bunny.yml", 1920, 1080),
     "spheres_on_plane": ("scenes/spheres_on_plane.yml", 720, 480),
     "bokeh_demo": ("scenes/bokeh_demo.yml", 1920, 1080),
+    "dragon": ("scenes/dragon.yml", 1920, 1080),        # synthetic 871k-triangle stand-in mesh (tools/make_assets.py)
+    "environment": ("scenes/environment.yml", 1920, 1080),
+    "doom": ("scenes/doom.yml", 1920, 1080),
 }
+ASSETS = {"dragon": ["dragon"], "environment": ["dragon", "hdri", "table"], "doom": ["doom"]}
+
+
+def ensure_assets(scene):
+    if scene in ASSETS:
+        sys.path.insert(0, str(ROOT / "tools"))
+        import make_assets
+
+        make_assets.ensure(*ASSETS[scene])
 METRIC = "path_samples_per_sec"
 UNIT = "samples/s"
 
@@ -327,6 +339,8 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if rank == 0:
+        ensure_assets(args.scene)
     if args.impl == "reference":
         run_reference(args, rank)
         return

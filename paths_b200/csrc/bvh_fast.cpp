@@ -221,6 +221,14 @@ uint32_t emit2(const std::vector<SNode> &sn, int node, FastTree &out, int32_t &c
 bool build_fast_tree(const HostScene &s, FastTree &out, std::string &err) {
     std::vector<Ref> refs;
     refs.reserve(s.prims.size());
+    // The slab test evaluates lo * (1/d) - o * (1/d): its error is about one ulp of the ORIGIN's coordinate, wherever the box is.
+    // Boxes are therefore grown by a few ulps of the scene's extent so that a ray that hits a triangle is never turned away by
+    // that triangle's own box.
+    double ext = 1.0;
+    if (s.bounds_lo.x <= s.bounds_hi.x)
+        ext = std::max({std::fabs(s.bounds_lo.x), std::fabs(s.bounds_hi.x), std::fabs(s.bounds_lo.y), std::fabs(s.bounds_hi.y),
+                        std::fabs(s.bounds_lo.z), std::fabs(s.bounds_hi.z), 1.0});
+    const float pad = (float)(ext * 4.76837158203125e-7); // 2^-21
     for (size_t i = 0; i < s.prims.size(); i++) {
         const HostPrim &p = s.prims[i];
         if (p.type == 1 && (p.box.lo.x == p.box.hi.x || p.box.lo.y == p.box.hi.y || p.box.lo.z == p.box.hi.z)) continue; // invisible (header)
@@ -237,6 +245,11 @@ bool build_fast_tree(const HostScene &s, FastTree &out, std::string &err) {
                 r.box.lo[2] = std::min(r.box.lo[2], fz); r.box.hi[2] = std::max(r.box.hi[2], fz);
             }
         }
+        if (p.type == 1)
+            for (int a = 0; a < 3; a++) {
+                r.box.lo[a] -= pad;
+                r.box.hi[a] += pad;
+            }
         for (int a = 0; a < 3; a++) r.c[a] = 0.5f * r.box.lo[a] + 0.5f * r.box.hi[a];
         r.prim = (uint32_t)i;
         refs.push_back(r);

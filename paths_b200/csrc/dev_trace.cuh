@@ -1,7 +1,7 @@
 // dev_trace.cuh -- ray / primitive intersection and BVH traversal on the device.
 //
 //   * trace_ref<>   f64, the reference's binary tree and visiting order (src/bvh.rs:78-140): bit-exact ids and distances.
-//   * trace_fast<>  production: f32 slab tests over 64-byte two-child nodes, f32 Moeller-Trumbore triangles,
+//   * trace_fast<>  production: f32 slab tests over 64-byte two-child nodes, watertight f32 triangles,
 //                   f64 spheres (the scenes' "planes" are spheres of radius 1e6: (l.oc)^2 - oc.oc + r^2 cancels ~1e12
 //                   against ~1e12, hopeless in f32), optional any-hit early-out for shadow rays.
 #pragma once
@@ -131,6 +131,68 @@ static __device__ __noinline__ Hit64 trace_ref(const DevScene &sc, D3v o, D3v d)
     return best;
 }
 
+
+// ------------------------------------------------------------------ watertight f32 ray / triangle test
+// Woop, Benthin, Wald 2013, with the axis permutation folded into two shear vectors p, q (both perpendicular to d):
+// x' = p . (v - o), y' = q . (v - o) put every vertex into the ray's own 2-D frame, where coordinates are of the size of
+// the triangle, not of its distance; edge functions U = Cx' By' - Cy' Bx' etc. are then evaluated with separately rounded
+// products (__fmul_rn, never contracted).  A vertex shared by two triangles gets bit-identical x', y' in both, so the
+// shared edge's function comes out EXACTLY negated: a ray cannot slip between two triangles that share an edge.
+// (Moeller-Trumbore in f32 lets ~3e-4 of the rays through an 871k-triangle mesh; the naive d . (B' x C') form is
+// watertight too but its barycentrics are off by eps * dist^2 / edge^2 -- 4e-2 on that mesh.)
+// Barycentrics are the reference's area ratios: bx = area(p,b,c) / area(a,b,c) (src/geom.rs:284-291).
+struct RayFrame {
+    float px, py, pz, qx, qy, qz;
+};
+__device__ __forceinline__ RayFrame ray_frame(float dx, float dy, float dz) {
+    RayFrame f;
+    float ax = fabsf(dx), ay = fabsf(dy), az = fabsf(dz);
+    if (az >= ax && az >= ay) { // kz = z
+        float iz = 1.0f / dz;
+        f.px = 1.0f; f.py = 0.0f; f.pz = -dx * iz;
+        f.qx = 0.0f; f.qy = 1.0f; f.qz = -dy * iz;
+    } else if (ay >= ax) { // kz = y
+        float iy = 1.0f / dy;
+        f.px = 0.0f; f.py = -dz * iy; f.pz = 1.0f;
+        f.qx = 1.0f; f.qy = -dx * iy; f.qz = 0.0f;
+    } else { // kz = x
+        float ix = 1.0f / dx;
+        f.px = -dy * ix; f.py = 1.0f; f.pz = 0.0f;
+        f.qx = -dz * ix; f.qy = 0.0f; f.qz = 1.0f;
+    }
+    return f;
+}
+struct TriHit {
+    float t, bx, by;
+};
+__device__ __forceinline__ bool triangle_hit_wt(float4 s0, float4 s1, float4 s2, const RayFrame &f, float ox, float oy, float oz, float dx, float dy,
+                                                float dz, float tmax, TriHit &h) {
+    float a0 = s0.x - ox, a1 = s0.y - oy, a2 = s0.z - oz;
+    float b0 = s1.x - ox, b1 = s1.y - oy, b2 = s1.z - oz;
+    float c0 = s2.x - ox, c1 = s2.y - oy, c2 = s2.z - oz;
+    // one fixed evaluation order for every vertex (explicit fma chain): a shared vertex must map to the same x', y' in both triangles
+    float Ax = __fmaf_rn(f.pz, a2, __fmaf_rn(f.py, a1, __fmul_rn(f.px, a0))), Ay = __fmaf_rn(f.qz, a2, __fmaf_rn(f.qy, a1, __fmul_rn(f.qx, a0)));
+    float Bx = __fmaf_rn(f.pz, b2, __fmaf_rn(f.py, b1, __fmul_rn(f.px, b0))), By = __fmaf_rn(f.qz, b2, __fmaf_rn(f.qy, b1, __fmul_rn(f.qx, b0)));
+    float Cx = __fmaf_rn(f.pz, c2, __fmaf_rn(f.py, c1, __fmul_rn(f.px, c0))), Cy = __fmaf_rn(f.qz, c2, __fmaf_rn(f.qy, c1, __fmul_rn(f.qx, c0)));
+    float U = __fmul_rn(Cx, By) - __fmul_rn(Cy, Bx);
+    float V = __fmul_rn(Ax, Cy) - __fmul_rn(Ay, Cx);
+    float W = __fmul_rn(Bx, Ay) - __fmul_rn(By, Ax);
+    float mn = fminf(U, fminf(V, W)), mx = fmaxf(U, fmaxf(V, W));
+    if (mn < 0.0f && mx > 0.0f) return false;
+    float det = U + V + W;
+    if (det == 0.0f) return false;
+    // distance from the plane equation with n = (b - a) x (c - a): its error grows like eps / cos(theta) only
+    float e1x = s1.x - s0.x, e1y = s1.y - s0.y, e1z = s1.z - s0.z, e2x = s2.x - s0.x, e2y = s2.y - s0.y, e2z = s2.z - s0.z;
+    float nx = e1y * e2z - e1z * e2y, ny = e1z * e2x - e1x * e2z, nz = e1x * e2y - e1y * e2x;
+    float t = (nx * a0 + ny * a1 + nz * a2) / (nx * dx + ny * dy + nz * dz);
+    if (!(t >= 0.0f && t < tmax)) return false;
+    float inv = 1.0f / det;
+    h.t = t;
+    h.bx = U * inv;
+    h.by = V * inv;
+    return true;
+}
+
 // ------------------------------------------------------------------ production traversal
 struct HitF {
     uint32_t prim;
@@ -151,6 +213,7 @@ template <bool ANY> __device__ __forceinline__ HitF trace_fast(const DevScene &s
     float idy = 1.0f / (fabsf(dy) > eps ? dy : copysignf(eps, dy));
     float idz = 1.0f / (fabsf(dz) > eps ? dz : copysignf(eps, dz));
     float oix = ox * idx, oiy = oy * idy, oiz = oz * idz;
+    const RayFrame frame = ray_frame(dx, dy, dz);
     int32_t stack[PATHS_FAST_STACK];
     int sp = 0;
     int32_t node = sc.fast_root;
@@ -209,21 +272,13 @@ template <bool ANY> __device__ __forceinline__ HitF trace_fast(const DevScene &s
                             if (ANY) return best;
                         }
                     }
-                } else { // triangle: v0 | e1 | e2, tag   (Moeller-Trumbore)
-                    float e1x = s1.x, e1y = s1.y, e1z = s1.z, e2x = s2.x, e2y = s2.y, e2z = s2.z;
-                    float px = dy * e2z - dz * e2y, py = dz * e2x - dx * e2z, pz = dx * e2y - dy * e2x;
-                    float det = e1x * px + e1y * py + e1z * pz;
-                    float inv = 1.0f / det;
-                    float tx = ox - s0.x, ty = oy - s0.y, tz = oz - s0.z;
-                    float u = (tx * px + ty * py + tz * pz) * inv;
-                    float qx = ty * e1z - tz * e1y, qy = tz * e1x - tx * e1z, qz = tx * e1y - ty * e1x;
-                    float v = (dx * qx + dy * qy + dz * qz) * inv;
-                    float t = (e2x * qx + e2y * qy + e2z * qz) * inv;
-                    if (u >= 0.0f && v >= 0.0f && u + v <= 1.0f && t >= 0.0f && t < best.t) {
-                        best.t = t;
+                } else { // triangle: v0 | v1 | v2, tag
+                    TriHit th;
+                    if (triangle_hit_wt(s0, s1, s2, frame, ox, oy, oz, dx, dy, dz, best.t, th)) {
+                        best.t = th.t;
                         best.prim = prim;
-                        best.bx = 1.0f - u - v; // weight of vertex a (geom.rs:289-291)
-                        best.by = u;            // weight of vertex b
+                        best.bx = th.bx;
+                        best.by = th.by;
                         if (ANY) return best;
                     }
                 }
@@ -286,6 +341,7 @@ struct TravF {
     template <bool ANY> __device__ __forceinline__ bool leaf(const float4 *__restrict__ leaves, int32_t *stack, uint32_t skip_prim) {
         uint32_t code = (uint32_t)~node;
         uint32_t first = code >> 3, cnt = (code & 7u) + 1u;
+        const RayFrame frame = ray_frame(dx, dy, dz); // recomputed per leaf visit: cheaper than six more live registers
         for (uint32_t k = 0; k < cnt; k++) {
             const float4 s0 = __ldg(leaves + 3 * (first + k));
             const float4 s1 = __ldg(leaves + 3 * (first + k) + 1);
@@ -307,17 +363,9 @@ struct TravF {
                     }
                 }
             } else {
-                float e1x = s1.x, e1y = s1.y, e1z = s1.z, e2x = s2.x, e2y = s2.y, e2z = s2.z;
-                float px = dy * e2z - dz * e2y, py = dz * e2x - dx * e2z, pz = dx * e2y - dy * e2x;
-                float det = e1x * px + e1y * py + e1z * pz;
-                float inv = 1.0f / det;
-                float tx = ox - s0.x, ty = oy - s0.y, tz = oz - s0.z;
-                float u = (tx * px + ty * py + tz * pz) * inv;
-                float qx = ty * e1z - tz * e1y, qy = tz * e1x - tx * e1z, qz = tx * e1y - ty * e1x;
-                float v = (dx * qx + dy * qy + dz * qz) * inv;
-                float tt = (e2x * qx + e2y * qy + e2z * qz) * inv;
-                if (u >= 0.0f && v >= 0.0f && u + v <= 1.0f && tt >= 0.0f && tt < t) {
-                    t = tt; prim = p; bx = 1.0f - u - v; by = u;
+                TriHit th;
+                if (triangle_hit_wt(s0, s1, s2, frame, ox, oy, oz, dx, dy, dz, t, th)) {
+                    t = th.t; prim = p; bx = th.bx; by = th.by;
                     if (ANY) return true;
                 }
             }

@@ -16,7 +16,7 @@ template <typename R> class RendererImpl : public RendererBase {
     uint32_t W_, H_, npix_, n_local_ = 0, spp_pass_ = 1, n_ctl_ = 0;
     size_t n_slots_max_ = 0;
     uint32_t samples_done_ = 0; // global samples per pixel issued so far (all ranks together)
-    int sm_count_ = 148, grid_trace_ = 0, grid_shade_ = 0, grid_stream_ = 0, variant_ = 1;
+    int sm_count_ = 148, grid_trace_ = 0, grid_shade_ = 0, grid_stream_ = 0, variant_ = 3;
     // device buffers
     R4 *sums_ = nullptr;
     uint32_t *pixels_ = nullptr; // tile shard: local -> global pixel

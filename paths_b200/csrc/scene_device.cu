@@ -112,11 +112,10 @@ SceneDevice *upload_scene(int device, const HostScene &hs, const RefTree *ref, c
             const HostPrim &p = hs.prims[prim];
             float4 *s = &leaves[3 * i];
             if (p.type == 1) {
-                D3 e1 = p.b - p.a, e2 = p.c - p.a;
                 uint32_t tag = prim;
                 s[0] = make_float4((float)p.a.x, (float)p.a.y, (float)p.a.z, 0.0f);
-                s[1] = make_float4((float)e1.x, (float)e1.y, (float)e1.z, 0.0f);
-                s[2] = make_float4((float)e2.x, (float)e2.y, (float)e2.z, 0.0f);
+                s[1] = make_float4((float)p.b.x, (float)p.b.y, (float)p.b.z, 0.0f);
+                s[2] = make_float4((float)p.c.x, (float)p.c.y, (float)p.c.z, 0.0f);
                 std::memcpy(&s[2].w, &tag, 4);
             } else {
                 double c[4] = {p.a.x, p.a.y, p.a.z, p.b.x};

@@ -1,0 +1,124 @@
+"""GPU parity on the large configs of BASELINE.json (dragon.yml, environment.yml, doom.yml).  The reference's /assets are
+git-ignored and absent, so seeded synthetic stand-ins of the same size are generated where the YAMLs expect them
+(tools/make_assets.py); the scene files themselves are the reference's, unmodified."""
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = Path(__file__).resolve().parent.parent
+
+
+@pytest.fixture(scope="module")
+def pb():
+    import paths_b200
+
+    if paths_b200.device_count() < 1:
+        pytest.fail("no CUDA device: the product has no CPU path")
+    sys.path.insert(0, str(ROOT / "tools"))
+    import make_assets
+
+    make_assets.ensure("dragon", "hdri", "doom", "table")
+    return paths_b200
+
+
+def relrmse(a, b):
+    return float(np.sqrt(np.mean((a - b) ** 2 / (b**2 + 0.01))))
+
+
+def test_dragon_fixed_rays(pb, oracle_mod):
+    # 871 207 primitives: ids and t bit-equal in f64 on camera rays and on incoherent surface rays; f32 ids equal except ties
+    osc, cam = oracle_mod.load_scene("scenes/dragon.yml", width=480, height=320)
+    gsc = pb.Scene.load("scenes/dragon.yml", width=480, height=320)
+    assert gsc.info["n_prims"] == osc.num_prims == 871207
+    o, d, _ = oracle_mod.camera_rays(cam, 4, 0)
+    p0, t0 = osc.trace_closest(o, d)
+    p1, t1 = gsc.find_intersection(o, d, precision=64)
+    assert np.array_equal(p0, p1)
+    hit = p0 != oracle_mod.MISS
+    assert hit.mean() > 0.9 and np.array_equal(t0[hit], t1[hit])
+    assert (p0 < 871200).mean() > 0.05  # the mesh is in view
+    rng = np.random.default_rng(1)
+    sel = np.nonzero(p0 < 871200)[0][:40000]
+    o2 = o[sel] + d[sel] * t0[sel, None]
+    d2 = rng.normal(size=o2.shape)
+    d2 /= np.linalg.norm(d2, axis=1, keepdims=True)
+    o2 += d2 * 1e-3
+    q0, s0 = osc.trace_closest(o2, d2)
+    q1, s1 = gsc.find_intersection(o2, d2, precision=64)
+    assert np.array_equal(q0, q1) and np.array_equal(s0[q0 != oracle_mod.MISS], s1[q0 != oracle_mod.MISS])
+    # production path
+    o32, d32 = o.astype(np.float32).astype(np.float64), d.astype(np.float32).astype(np.float64)
+    r0, u0, b0 = osc.trace_closest(o32, d32, want_bary=True)
+    r1, u1 = gsc.find_intersection(o, d, precision=32)
+    same = r0 == r1
+    assert same.mean() > 0.995  # 871k sub-pixel triangles: ~1e-3 of the rays pass within f32 position error of an edge
+    h = same & (r0 != oracle_mod.MISS)
+    assert np.all(np.abs(u1[h] - u0[h]) <= 1e-4 * np.abs(u0[h]))
+    # every id difference must be explained by the oracle: the two candidates are a tie within 1e-4 relative (shared edge, the
+    # watertight test may pick either neighbour), or the oracle's own hit lies within f32 position error of a triangle edge
+    # (silhouette: |o| * 2^-23 against ~0.01-long edges is about 1e-3 in barycentric units)
+    unexplained = 0
+    for i in np.nonzero(~same)[0]:
+        ta = osc.intersect_prim(r0[i], o32[i], d32[i]) if r0[i] != oracle_mod.MISS else None
+        tb = osc.intersect_prim(r1[i], o32[i], d32[i]) if r1[i] != oracle_mod.MISS else None
+        tie = ta is not None and tb is not None and abs(ta - tb) <= 1e-4 * abs(ta)
+        near_edge = r0[i] != oracle_mod.MISS and r0[i] < 871200 and b0[i].min() < 2e-3
+        if not (tie or near_edge):
+            unexplained += 1
+    assert unexplained == 0, f"{unexplained} of {(~same).sum()} id differences are neither ties nor edge grazes"
+
+
+def test_dragon_image_f32(pb, oracle_mod):
+    # NEE to an area light, metallic gloss mesh, five 1e6-radius wall spheres
+    osc, cam = oracle_mod.load_scene("scenes/dragon.yml", width=120, height=80)
+    gsc = pb.Scene.load("scenes/dragon.yml", width=120, height=80)
+    spp = 16
+    r = pb.Renderer(cam, gsc, precision=32, seed=4)
+    r.render_samples(spp)
+    g = r.sums()[..., :3] / spp
+    st = r.stats()
+    r.shutdown()
+    a = osc.render(cam, 4, 0, spp)[0] / spp
+    b = osc.render(cam, 5, 0, spp)[0] / spp
+    sigma0 = relrmse(a, b)
+    assert relrmse(g, a) <= 0.5 * sigma0 and relrmse(g, b) <= 1.15 * sigma0
+    assert st["shadow_rays"] > 0 and st["bad_samples"] == 0
+
+
+def test_doom_auto_precision_is_f64_and_follows_oracle(pb, oracle_mod):
+    # coordinates +-700: the scene resolves to the f64 instantiation; per-vertex colours; big area light
+    osc, cam = oracle_mod.load_scene("scenes/doom.yml", width=72, height=48)
+    gsc = pb.Scene.load("scenes/doom.yml", width=72, height=48)
+    assert gsc.info["auto_precision"] == 64
+    r = pb.Renderer(cam, gsc, seed=6)  # PRECISION_AUTO
+    _, _, eb = r.device_sums()
+    assert eb == 8
+    r.render_samples(3)
+    s = r.sums()
+    r.shutdown()
+    sums, counts, ctr = osc.render(cam, 6, 0, 3)
+    close = np.all(np.abs(s[..., :3] - sums) <= 1e-9 * (np.abs(sums) + 1e-3), axis=-1)
+    assert close.mean() >= 0.995 and sums.max() > 0
+
+
+def test_environment_hdri_and_auto_material(pb, oracle_mod):
+    # HDRI lookup on a miss (scene.rs:95-111), `material: Auto` from the OBJ's MTL, smooth-normal dragon
+    osc, cam = oracle_mod.load_scene("scenes/environment.yml", width=96, height=64)
+    gsc = pb.Scene.load("scenes/environment.yml", width=96, height=64)
+    r = pb.Renderer(cam, gsc, precision=64, seed=8)
+    r.render_samples(2)
+    s = r.sums()
+    r.shutdown()
+    sums, _, _ = osc.render(cam, 8, 0, 2)
+    close = np.all(np.abs(s[..., :3] - sums) <= 1e-9 * (np.abs(sums) + 1e-3), axis=-1)
+    assert close.mean() >= 0.995
+    r = pb.Renderer(cam, gsc, precision=32, seed=8)
+    r.render_samples(16)
+    g = r.sums()[..., :3] / 16
+    r.shutdown()
+    a = osc.render(cam, 8, 0, 16)[0] / 16
+    b = osc.render(cam, 9, 0, 16)[0] / 16
+    assert relrmse(g, a) <= 0.5 * relrmse(a, b)

@@ -5,6 +5,7 @@ import time
 from pathlib import Path
 
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+sys.path.insert(0, str(Path(__file__).resolve().parent))
 import paths_b200 as pb  # noqa: E402
 
 scene = sys.argv[1] if len(sys.argv) > 1 else "scenes/teapot.yml"
@@ -13,6 +14,9 @@ W = int(sys.argv[3]) if len(sys.argv) > 3 else 1920
 H = int(sys.argv[4]) if len(sys.argv) > 4 else 1080
 prec = int(sys.argv[5]) if len(sys.argv) > 5 else 32
 spass = int(sys.argv[6]) if len(sys.argv) > 6 else 0
+import make_assets  # noqa: E402
+
+make_assets.ensure("dragon", "hdri", "doom", "table")
 sc = pb.Scene.load(scene, width=W, height=H)
 for timed in (False, True):
     r = pb.Renderer(sc.camera, sc, precision=prec, seed=1, time_kernels=timed, samples_per_pass=spass)
