@@ -46,6 +46,28 @@ __device__ __forceinline__ bool isnan_(double a) { return isnan(a); }
 
 // vector.rs:39-41: normed() divides by sqrt(magnitude()), magnitude() being the SQUARED length (vector.rs:27-29)
 template <typename R> __device__ __forceinline__ V3<R> normed(V3<R> a) { return a / sqrt_(dot(a, a)); }
+// production (f32) shortcuts: one reciprocal (square root) and three multiplies instead of three IEEE divisions; the f64
+// instantiation keeps the reference's operations
+__device__ __forceinline__ V3<float> operator/(V3<float> a, float s) {
+    float r = 1.0f / s;
+    return mk3<float>(a.x * r, a.y * r, a.z * r);
+}
+template <> __device__ __forceinline__ V3<float> normed<float>(V3<float> a) {
+    float r = rsqrtf(a.x * a.x + a.y * a.y + a.z * a.z);
+    return mk3<float>(a.x * r, a.y * r, a.z * r);
+}
+// x^5 (material.rs:304 powf(5.0)) and sin/cos of 2*pi*v (geom.rs:15, geom.rs:150)
+__device__ __forceinline__ double pow5_(double x) { return pow(x, 5.0); }
+__device__ __forceinline__ float pow5_(float x) {
+    float x2 = x * x;
+    return x2 * x2 * x;
+}
+__device__ __forceinline__ void sincos_2pi(double v, double *s, double *c) {
+    double theta = 2.0 * 3.14159265358979323846 * v;
+    *s = sin(theta);
+    *c = cos(theta);
+}
+__device__ __forceinline__ void sincos_2pi(float v, float *s, float *c) { sincospif(2.0f * v, s, c); }
 template <typename R> __device__ __forceinline__ R vmax3(V3<R> a) { return fmax_(a.x, fmax_(a.y, a.z)); } // vector.rs:31-33
 template <typename R> __device__ __forceinline__ R vmin3(V3<R> a) { return fmin_(a.x, fmin_(a.y, a.z)); } // vector.rs:35-37
 // colour.rs:38-41 (plain comparisons, not fmax)

@@ -86,10 +86,9 @@ template <typename R> __device__ __forceinline__ void cmj(uint32_t s, uint32_t m
 template <typename R> __device__ __forceinline__ void cmj_disk(uint32_t s, uint32_t m, uint32_t n, uint32_t p, R &dx, R &dy) {
     R x, y;
     cmj<R>(s, m, n, p, x, y);
-    R theta = R(2.0) * Consts<R>::pi() * x;
     R r = sqrt_(y);
     R sn, cs;
-    sincos_(theta, &sn, &cs);
+    sincos_2pi(x, &sn, &cs); // theta = 2 pi x
     dx = r * cs;
     dy = r * sn;
 }

@@ -53,9 +53,8 @@ template <typename R> __device__ __forceinline__ V3<R> reflect(V3<R> vector, V3<
 // geom.rs:10-24 (note y = 1 - u, not sqrt(1 - u): kept)
 template <typename R> __device__ __forceinline__ V3<R> lambert_direction(V3<R> normal, R u, R v) { // material.rs:224-231
     R r = sqrt_(u);
-    R theta = R(2.0) * Consts<R>::pi() * v;
     R sn, cs;
-    sincos_(theta, &sn, &cs);
+    sincos_2pi(v, &sn, &cs); // theta = 2 pi v
     V3<R> rd = mk3<R>(r * cs, R(1.0) - u, r * sn);
     return normed(to_world(rd, normal));
 }
@@ -65,7 +64,7 @@ template <typename R> __device__ __forceinline__ V3<R> lambert_brdf(V3<R> albedo
 }
 template <typename R> __device__ __forceinline__ R schlick(R r0, V3<R> vec_out, V3<R> normal) { // :303-305
     R cos_theta = dot(vec_out, normal);
-    return r0 + (R(1.0) - r0) * pow_(R(1.0) - cos_theta, R(5.0));
+    return r0 + (R(1.0) - r0) * pow5_(R(1.0) - cos_theta);
 }
 template <typename R> __device__ __forceinline__ R beckmann_ndf(R m, V3<R> n, V3<R> h) { // :436-447
     R alpha = acos_(dot(h, n));
@@ -182,11 +181,10 @@ template <typename R> __device__ __forceinline__ void light_sample(const DevLigh
         return;
     }
     R radius = R(l.radius);
-    R theta = R(2.0) * Consts<R>::pi() * u;
     R phi = acos_(R(2.0) * v - R(1.0));
     R sp, cp, st, ct;
     sincos_(phi, &sp, &cp);
-    sincos_(theta, &st, &ct);
+    sincos_2pi(u, &st, &ct); // theta = 2 pi u
     V3<R> n = mk3<R>(sp * ct, sp * st, cp);
     V3<R> point = lv + n * radius;
     V3<R> out_vec = from - point;

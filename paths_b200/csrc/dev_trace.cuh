@@ -339,7 +339,14 @@ struct TravF {
     }
     // one leaf (node < 0, not DONE): tests its primitives, then pops.  Returns true when ANY and something was hit.
     template <bool ANY> __device__ __forceinline__ bool leaf(const float4 *__restrict__ leaves, int32_t *stack, uint32_t skip_prim) {
-        uint32_t code = (uint32_t)~node;
+        if (leaf_test<ANY>(leaves, node, skip_prim)) return true;
+        node = sp > 0 ? stack[--sp] : PATHS_TRAV_DONE;
+        return false;
+    }
+    __device__ __forceinline__ int32_t pop(int32_t *stack) { return sp > 0 ? stack[--sp] : PATHS_TRAV_DONE; }
+    // tests the primitives of leaf `leaf_code` (< 0) without touching the traversal position
+    template <bool ANY> __device__ __forceinline__ bool leaf_test(const float4 *__restrict__ leaves, int32_t leaf_code, uint32_t skip_prim) {
+        uint32_t code = (uint32_t)~leaf_code;
         uint32_t first = code >> 3, cnt = (code & 7u) + 1u;
         const RayFrame frame = ray_frame(dx, dy, dz); // recomputed per leaf visit: cheaper than six more live registers
         for (uint32_t k = 0; k < cnt; k++) {
@@ -370,7 +377,6 @@ struct TravF {
                 }
             }
         }
-        node = sp > 0 ? stack[--sp] : PATHS_TRAV_DONE;
         return false;
     }
 };

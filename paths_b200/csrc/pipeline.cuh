@@ -96,9 +96,9 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
                                            uint32_t k0, uint32_t k1, uint32_t max_bounces, unsigned long long *totals, ShadeOut<R> &out) {
     typedef typename Vec4T<R>::type R4;
     const V3<R> black = mk3<R>(R(0), R(0), R(0));
-    R4 o4 = ps.ray_o[slot], d4 = ps.ray_d[slot], h4 = ps.hit[slot], t4 = ps.thr[slot], c4 = ps.col[slot];
+    R4 o4 = ps.ray_o[slot], d4 = ps.ray_d[slot], h4 = ps.hit[slot], t4 = ps.thr[slot];
     V3<R> ro = mk3<R>(o4.x, o4.y, o4.z), rd = mk3<R>(d4.x, d4.y, d4.z);
-    V3<R> throughput = mk3<R>(t4.x, t4.y, t4.z), colour = mk3<R>(c4.x, c4.y, c4.z);
+    V3<R> throughput = mk3<R>(t4.x, t4.y, t4.z);
     uint32_t flags = real_to_bits(t4.w);
     uint32_t loops = flags & 0xFFu;
     bool last_specular = (flags & PATHS_FLAG_SPECULAR) != 0;
@@ -107,6 +107,8 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
     out.shadow = false;
 
     if (prim == 0xFFFFFFFFu) { // trace.rs:20-23
+        R4 c4 = ps.col[slot]; // the radiance record is only touched by the branches that add light
+        V3<R> colour = mk3<R>(c4.x, c4.y, c4.z);
         colour = colour + throughput * sky_light<R>(sc, neg(rd));
         ps.col[slot] = mk4(colour.x, colour.y, colour.z, c4.w);
         return;
@@ -145,6 +147,8 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
     if (is_light) { // trace.rs:31-41
         if (last_specular) {
             const DevLight &l = sc.lights[meta.y];
+            R4 c4 = ps.col[slot];
+            V3<R> colour = mk3<R>(c4.x, c4.y, c4.z);
             colour = colour + throughput * mk3<R>(R(l.colour[0]), R(l.colour[1]), R(l.colour[2])) * R(l.intensity);
             if (col_bad(colour)) atomicAdd(totals + 2, 1ull);
             ps.col[slot] = mk4(colour.x, colour.y, colour.z, c4.w);
@@ -160,8 +164,12 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
         V3<R> cc = mk3<R>(R(vc[3 * face[2]]), R(vc[3 * face[2] + 1]), R(vc[3 * face[2] + 2]));
         mat.m.albedo = ac * bx + bc * by + cc * bz;
     }
-    U4 r0 = philox4x32_10(pixel, S, loops * 2u, PATHS_TAG_PATH, k0, k1);
-    U4 r1 = philox4x32_10(pixel, S, loops * 2u + 1u, PATHS_TAG_PATH, k0, k1);
+    // block 0 = {light choice, light u, light v, gloss choice}; block 1 = {hemisphere u, v, roulette, -}: generated only when read
+    U4 r0, r1;
+    r0.v[0] = r0.v[1] = r0.v[2] = r0.v[3] = 0u;
+    r1 = r0;
+    if (sc.n_lights > 0 || mat.m.type == 2) r0 = philox4x32_10(pixel, S, loops * 2u, PATHS_TAG_PATH, k0, k1);
+    if (loops >= 2 || mat.m.type == 0 || mat.m.type == 2) r1 = philox4x32_10(pixel, S, loops * 2u + 1u, PATHS_TAG_PATH, k0, k1);
     V3<R> vec_out = neg(rd);
     V3<R> new_origin = location + normal * R(0.0001); // trace.rs:57,89
 
@@ -340,6 +348,66 @@ __global__ void __launch_bounds__(128) k_extend_refill(DevScene sc, PathState<fl
 #pragma unroll 1
                 for (int k = 0; k < 3 && tv.node >= 0; k++) tv.inner(nodes, stack);
                 if (tv.node < 0 && tv.node != PATHS_TRAV_DONE) tv.leaf<false>(leaves, stack, 0xFFFFFFFFu);
+                if (tv.node == PATHS_TRAV_DONE) {
+                    ps.hit[slot] = make_float4(__uint_as_float(tv.prim), tv.t, tv.bx, tv.by);
+                    has = false;
+                }
+            }
+        }
+    }
+}
+
+// Speculative variant: a lane that reaches a leaf parks it and keeps descending from its stack, so that the leaf phase of a
+// round runs with as many lanes as possible (ncu on k_extend_refill: triangle tests ran with 6 of 32 lanes).
+template <int ROUNDS, int MIN_REFILL, int KI>
+__global__ void __launch_bounds__(128) k_extend_spec(DevScene sc, PathState<float4> ps, const uint32_t *queue, const uint32_t *count_ptr,
+                                                     uint32_t *cursor) {
+    const uint32_t count = *count_ptr;
+    const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    const float4 *__restrict__ nodes = sc.fast_nodes;
+    const float4 *__restrict__ leaves = sc.fast_leaves;
+    int32_t stack[PATHS_FAST_STACK];
+    TravF tv;
+    tv.node = PATHS_TRAV_DONE;
+    bool has = false, exhausted = false;
+    uint32_t slot = 0;
+    int32_t pend = 0; // parked leaf code (< 0) or 0
+    for (;;) {
+        unsigned idle = __ballot_sync(PATHS_FULL_MASK, !has);
+        int n = __popc(idle);
+        if (!exhausted && n >= MIN_REFILL) {
+            int leader = __ffs(idle) - 1;
+            uint32_t base = 0;
+            if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)n);
+            base = __shfl_sync(PATHS_FULL_MASK, base, leader);
+            if (!has) {
+                uint32_t i = base + __popc(idle & lt);
+                if (i < count) {
+                    slot = queue ? queue[i] : i;
+                    float4 o = ps.ray_o[slot], d = ps.ray_d[slot];
+                    tv.init(o.x, o.y, o.z, d.x, d.y, d.z, __int_as_float(0x7f800000), sc.fast_root);
+                    pend = 0;
+                    has = true;
+                }
+            }
+            exhausted = base + (uint32_t)n >= count;
+        }
+        if (!__any_sync(PATHS_FULL_MASK, has)) break;
+#pragma unroll 1
+        for (int r = 0; r < ROUNDS; r++) {
+            if (has) {
+#pragma unroll 1
+                for (int k = 0; k < KI; k++) {
+                    if (tv.node >= 0) tv.inner(nodes, stack);
+                    if (tv.node < 0 && tv.node != PATHS_TRAV_DONE && pend == 0) {
+                        pend = tv.node;
+                        tv.node = tv.pop(stack);
+                    }
+                }
+                if (pend != 0) {
+                    tv.leaf_test<false>(leaves, pend, 0xFFFFFFFFu);
+                    pend = 0;
+                }
                 if (tv.node == PATHS_TRAV_DONE) {
                     ps.hit[slot] = make_float4(__uint_as_float(tv.prim), tv.t, tv.bx, tv.by);
                     has = false;
