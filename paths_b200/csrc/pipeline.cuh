@@ -12,6 +12,13 @@
 namespace paths {
 
 #define PATHS_FULL_MASK 0xFFFFFFFFu
+// resident 128-thread blocks per SM the register allocator must leave room for (65536 / (128 * regs))
+#ifndef PATHS_LB_EXTEND
+#define PATHS_LB_EXTEND 8
+#endif
+#ifndef PATHS_LB_SHADE
+#define PATHS_LB_SHADE 5
+#endif
 #define PATHS_FLAG_SPECULAR 0x100u
 
 template <typename R> struct IsF64 {
@@ -226,7 +233,7 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
 }
 
 template <typename R>
-__global__ void __launch_bounds__(128) k_shade(DevScene sc, PathState<typename Vec4T<R>::type> ps, ShardInfo shard, uint32_t s_base, uint32_t k0,
+__global__ void __launch_bounds__(128, PATHS_LB_SHADE) k_shade(DevScene sc, PathState<typename Vec4T<R>::type> ps, ShardInfo shard, uint32_t s_base, uint32_t k0,
                                                uint32_t k1, uint32_t max_bounces, const uint32_t *queue, uint32_t *queue_next,
                                                const uint32_t *count_ptr, uint32_t *next_count, uint32_t *shadow_count, uint32_t *cursor,
                                                unsigned long long *totals) {
@@ -311,7 +318,7 @@ __global__ void __launch_bounds__(128) k_shadow(DevScene sc, PathState<typename 
 // instead of waiting for the slowest ray of a batch of 32.  ROUNDS bounded traversal rounds run between two refill checks;
 // one round = up to three inner nodes, then at most one leaf.
 template <int ROUNDS, int MIN_REFILL>
-__global__ void __launch_bounds__(128) k_extend_refill(DevScene sc, PathState<float4> ps, const uint32_t *queue, const uint32_t *count_ptr,
+__global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend_refill(DevScene sc, PathState<float4> ps, const uint32_t *queue, const uint32_t *count_ptr,
                                                        uint32_t *cursor) {
     const uint32_t count = *count_ptr;
     const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
@@ -418,7 +425,7 @@ __global__ void __launch_bounds__(128) k_extend_spec(DevScene sc, PathState<floa
 }
 
 template <int ROUNDS, int MIN_REFILL>
-__global__ void __launch_bounds__(128) k_shadow_refill(DevScene sc, PathState<float4> ps, const uint32_t *count_ptr, uint32_t *cursor,
+__global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_shadow_refill(DevScene sc, PathState<float4> ps, const uint32_t *count_ptr, uint32_t *cursor,
                                                        unsigned long long *totals) {
     const uint32_t count = *count_ptr;
     const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;

@@ -162,7 +162,8 @@ template <typename R> class RendererImpl : public RendererBase {
         if (const char *v = getenv("PATHS_EXTEND_VARIANT")) variant_ = atoi(v); // development switch between traversal kernels
         // ---- persistent grids: every SM full
         int bps = 0;
-        PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_extend<R>, 128, 0));
+        if constexpr (IsF64<R>::value) PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_extend<R>, 128, 0));
+        else PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_extend_refill<4, 16>, 128, 0));
         grid_trace_ = sm_count_ * std::max(bps, 1);
         PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_shade<R>, 128, 0));
         grid_shade_ = sm_count_ * std::max(bps, 1);
