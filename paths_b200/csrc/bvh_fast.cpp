@@ -216,6 +216,55 @@ uint32_t emit2(const std::vector<SNode> &sn, int node, FastTree &out, int32_t &c
     return 1 + std::max(dl, dr);
 }
 
+// Collapse to four-wide nodes: a node's children are its binary children, with the child of largest surface area replaced by
+// its own two children until four slots are used (or only leaves remain).
+uint32_t emit4(const std::vector<SNode> &sn, int node, FastTree &out, int32_t &code) {
+    const SNode &n = sn[node];
+    if (n.count > 0) {
+        code = leaf_code(n.first, n.count);
+        return 1;
+    }
+    int kids[4];
+    int nk = 0;
+    kids[nk++] = n.left;
+    kids[nk++] = n.right;
+    while (nk < 4) {
+        int best = -1;
+        float best_area = -1.0f;
+        for (int i = 0; i < nk; i++) {
+            const SNode &c = sn[kids[i]];
+            if (c.count == 0 && c.box.half_area() > best_area) {
+                best_area = c.box.half_area();
+                best = i;
+            }
+        }
+        if (best < 0) break;
+        int open = kids[best];
+        kids[best] = sn[open].left;
+        kids[nk++] = sn[open].right;
+    }
+    int32_t me = (int32_t)out.nodes4.size();
+    out.nodes4.push_back(FastNode4());
+    code = me;
+    int32_t codes[4] = {0, 0, 0, 0};
+    uint32_t depth = 0;
+    for (int i = 0; i < nk; i++) depth = std::max(depth, emit4(sn, kids[i], out, codes[i]));
+    FastNode4 &fn = out.nodes4[me];
+    std::memset(&fn, 0, sizeof(fn));
+    for (int i = 0; i < 4; i++) {
+        if (i < nk) {
+            const FBox &b = sn[kids[i]].box;
+            fn.lox[i] = b.lo[0]; fn.hix[i] = b.hi[0]; fn.loy[i] = b.lo[1]; fn.hiy[i] = b.hi[1]; fn.loz[i] = b.lo[2]; fn.hiz[i] = b.hi[2];
+            fn.child[i] = codes[i];
+        } else {
+            fn.lox[i] = fn.loy[i] = fn.loz[i] = std::numeric_limits<float>::infinity();
+            fn.hix[i] = fn.hiy[i] = fn.hiz[i] = -std::numeric_limits<float>::infinity();
+            fn.child[i] = 0x7FFFFFFF; // PATHS_CHILD_EMPTY
+        }
+    }
+    return 1 + depth;
+}
+
 } // namespace
 
 bool build_fast_tree(const HostScene &s, FastTree &out, std::string &err) {
@@ -265,9 +314,19 @@ bool build_fast_tree(const HostScene &s, FastTree &out, std::string &err) {
         }
         fn.i0 = fn.i1 = 0;
         out.nodes.push_back(fn);
-        out.root = 0;
+        out.root = (int32_t)0x80000000; // PATHS_TRAV_DONE: the kernels finish at once
         for (int a = 0; a < 6; a++) out.root_box[a] = (a < 3) ? std::numeric_limits<float>::infinity() : -std::numeric_limits<float>::infinity();
         out.depth = 1;
+        FastNode4 f4;
+        std::memset(&f4, 0, sizeof(f4));
+        for (int i = 0; i < 4; i++) {
+            f4.lox[i] = f4.loy[i] = f4.loz[i] = std::numeric_limits<float>::infinity();
+            f4.hix[i] = f4.hiy[i] = f4.hiz[i] = -std::numeric_limits<float>::infinity();
+        }
+        for (int i = 0; i < 4; i++) f4.child[i] = 0x7FFFFFFF;
+        out.nodes4.push_back(f4);
+        out.root4 = (int32_t)0x80000000;
+        out.depth4 = 1;
         (void)err;
         return true;
     }
@@ -281,6 +340,23 @@ bool build_fast_tree(const HostScene &s, FastTree &out, std::string &err) {
     for (int a = 0; a < 3; a++) {
         out.root_box[a] = sn[root].box.lo[a];
         out.root_box[3 + a] = sn[root].box.hi[a];
+    }
+    out.nodes4.reserve(refs.size() / 2 + 1);
+    out.depth4 = emit4(sn, root, out, out.root4);
+    if (out.root4 < 0) { // a single leaf: one node with three empty slots
+        FastNode4 f4;
+        std::memset(&f4, 0, sizeof(f4));
+        for (int i = 0; i < 4; i++) {
+            f4.lox[i] = f4.loy[i] = f4.loz[i] = std::numeric_limits<float>::infinity();
+            f4.hix[i] = f4.hiy[i] = f4.hiz[i] = -std::numeric_limits<float>::infinity();
+        }
+        f4.lox[0] = sn[root].box.lo[0]; f4.hix[0] = sn[root].box.hi[0]; f4.loy[0] = sn[root].box.lo[1];
+        f4.hiy[0] = sn[root].box.hi[1]; f4.loz[0] = sn[root].box.lo[2]; f4.hiz[0] = sn[root].box.hi[2];
+        for (int i = 1; i < 4; i++) f4.child[i] = 0x7FFFFFFF;
+        f4.child[0] = out.root4;
+        out.nodes4.push_back(f4);
+        out.root4 = 0;
+        out.depth4 = 2;
     }
     if (out.root < 0) {
         // a single leaf: wrap it in one inner node whose second child is empty

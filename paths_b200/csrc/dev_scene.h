@@ -52,6 +52,10 @@ struct DevScene {
     const float4 *fast_nodes;
     const float4 *fast_leaves;
     int32_t fast_root;
+    // ---- the same tree, four-wide: 8 float4 (128 B) per node = {lo.x, hi.x, lo.y, hi.y, lo.z, hi.z}[4 children], child codes, pad
+    const float4 *fast4_nodes;
+    int32_t fast4_root;
+    uint32_t fast4_depth;
     // ---- shading tables
     const DevObject *objects;
     const DevLight *lights;

@@ -217,6 +217,7 @@ template <bool ANY> __device__ __forceinline__ HitF trace_fast(const DevScene &s
     int32_t stack[PATHS_FAST_STACK];
     int sp = 0;
     int32_t node = sc.fast_root;
+    if (node == (int32_t)0x80000000) return best; // empty tree
     const float4 *__restrict__ nodes = sc.fast_nodes;
     const float4 *__restrict__ leaves = sc.fast_leaves;
     for (;;) {
@@ -293,6 +294,7 @@ template <bool ANY> __device__ __forceinline__ HitF trace_fast(const DevScene &s
 // The same arithmetic as trace_fast, cut into bounded steps so that a warp can hand a finished lane a new ray instead of
 // idling until its slowest ray ends (ncu on the batch-of-32 version: 7-9 of 32 threads active per instruction on bounce rays).
 #define PATHS_TRAV_DONE ((int32_t)0x80000000)
+#define PATHS_CHILD_EMPTY ((int32_t)0x7FFFFFFF)
 
 struct TravF {
     float ox, oy, oz, dx, dy, dz, idx, idy, idz, oix, oiy, oiz;
@@ -379,6 +381,57 @@ struct TravF {
         }
         return false;
     }
+};
+
+// ------------------------------------------------------------------ four-wide traversal, stack in shared memory
+// Node = one 128-byte line: six float4 rows {lo.x, hi.x, lo.y, hi.y, lo.z, hi.z} over the four children + their codes.
+// Hit children are sorted by entry distance with a 5-exchange network; the nearest is entered, the rest are pushed far-first.
+// The stack lives in shared memory as stack[level * blockDim.x + thread] (conflict-free); its depth is sized by the host from
+// the tree (3 * depth + 1 entries always suffice), so there is no overflow path.
+struct TravF4 : TravF {
+    __device__ __forceinline__ void inner4(const float4 *__restrict__ nodes4, int32_t *sstack, uint32_t stride) {
+        const float4 *n = nodes4 + 8 * (size_t)node;
+        const float4 lox = __ldg(n), hix = __ldg(n + 1), loy = __ldg(n + 2), hiy = __ldg(n + 3), loz = __ldg(n + 4), hiz = __ldg(n + 5);
+        const float4 chf = __ldg(n + 6);
+        const float inf = __int_as_float(0x7f800000);
+        float k0, k1, k2, k3;
+#define PATHS_BOX4(c, key)                                                                                                  \
+    {                                                                                                                       \
+        float x0 = lox.c * idx - oix, x1 = hix.c * idx - oix, y0 = loy.c * idy - oiy, y1 = hiy.c * idy - oiy;               \
+        float z0 = loz.c * idz - oiz, z1 = hiz.c * idz - oiz;                                                               \
+        float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.0f));                                  \
+        float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), t)) * 1.0000004f;                        \
+        key = tn <= tf ? tn : inf;                                                                                          \
+    }
+        PATHS_BOX4(x, k0)
+        PATHS_BOX4(y, k1)
+        PATHS_BOX4(z, k2)
+        PATHS_BOX4(w, k3)
+#undef PATHS_BOX4
+        int32_t c0 = __float_as_int(chf.x), c1 = __float_as_int(chf.y), c2 = __float_as_int(chf.z), c3 = __float_as_int(chf.w);
+        // unused slots (an inverted box still passes a min/max slab test) are marked by their code
+        k0 = c0 == PATHS_CHILD_EMPTY ? inf : k0;
+        k1 = c1 == PATHS_CHILD_EMPTY ? inf : k1;
+        k2 = c2 == PATHS_CHILD_EMPTY ? inf : k2;
+        k3 = c3 == PATHS_CHILD_EMPTY ? inf : k3;
+#define PATHS_CE(ka, ca, kb, cb)          \
+    if (kb < ka) {                        \
+        float tk = ka; ka = kb; kb = tk;  \
+        int32_t tc = ca; ca = cb; cb = tc;\
+    }
+        PATHS_CE(k0, c0, k1, c1)
+        PATHS_CE(k2, c2, k3, c3)
+        PATHS_CE(k0, c0, k2, c2)
+        PATHS_CE(k1, c1, k3, c3)
+        PATHS_CE(k1, c1, k2, c2)
+#undef PATHS_CE
+        if (k3 < inf) sstack[(sp++) * stride] = c3;
+        if (k2 < inf) sstack[(sp++) * stride] = c2;
+        if (k1 < inf) sstack[(sp++) * stride] = c1;
+        if (k0 < inf) node = c0;
+        else node = sp > 0 ? sstack[(--sp) * stride] : PATHS_TRAV_DONE;
+    }
+    __device__ __forceinline__ int32_t pop4(const int32_t *sstack, uint32_t stride) { return sp > 0 ? sstack[(--sp) * stride] : PATHS_TRAV_DONE; }
 };
 
 } // namespace paths

@@ -101,12 +101,21 @@ struct FastNode2 { // 64 B, both children boxes in the parent
     int32_t i0, i1; // >= 0 inner; < 0 leaf code: ~((first << 3) | (count - 1))
     int32_t pad[2];
 };
+struct FastNode4 { // 128 B = one cache line: child boxes as SoA rows, then the four child codes
+    float lox[4], hix[4], loy[4], hiy[4], loz[4], hiz[4];
+    int32_t child[4]; // >= 0 inner; < 0 leaf code; empty slots carry an inverted (never hit) box
+    int32_t pad[4];
+};
 struct FastTree {
     std::vector<FastNode2> nodes;
     int32_t root = 0;
     float root_box[6];
     std::vector<uint32_t> leaf_prims; // prim ids in leaf order
     uint32_t depth = 0;
+    // the same tree collapsed to four-wide nodes (every other level of the binary tree is folded into its parent)
+    std::vector<FastNode4> nodes4;
+    int32_t root4 = 0;
+    uint32_t depth4 = 0;
 };
 
 struct HostScene {

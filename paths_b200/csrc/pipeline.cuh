@@ -488,6 +488,128 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_shadow_refill(DevScene
     }
 }
 
+// ------------------------------------------------------------------ four-wide extend / shadow (lane refill, shared-memory stack)
+template <int ROUNDS, int MIN_REFILL, int KI>
+__global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend4(DevScene sc, PathState<float4> ps, const uint32_t *queue, const uint32_t *count_ptr,
+                                                                  uint32_t *cursor) {
+    extern __shared__ int32_t smem_stack[];
+    int32_t *sstack = smem_stack + threadIdx.x;
+    const uint32_t stride = blockDim.x;
+    const uint32_t count = *count_ptr;
+    const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    const float4 *__restrict__ nodes4 = sc.fast4_nodes;
+    const float4 *__restrict__ leaves = sc.fast_leaves;
+    TravF4 tv;
+    tv.node = PATHS_TRAV_DONE;
+    bool has = false, exhausted = false;
+    uint32_t slot = 0;
+    for (;;) {
+        unsigned idle = __ballot_sync(PATHS_FULL_MASK, !has);
+        int n = __popc(idle);
+        if (!exhausted && n >= MIN_REFILL) {
+            int leader = __ffs(idle) - 1;
+            uint32_t base = 0;
+            if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)n);
+            base = __shfl_sync(PATHS_FULL_MASK, base, leader);
+            if (!has) {
+                uint32_t i = base + __popc(idle & lt);
+                if (i < count) {
+                    slot = queue ? queue[i] : i;
+                    float4 o = ps.ray_o[slot], d = ps.ray_d[slot];
+                    tv.init(o.x, o.y, o.z, d.x, d.y, d.z, __int_as_float(0x7f800000), sc.fast4_root);
+                    has = true;
+                }
+            }
+            exhausted = base + (uint32_t)n >= count;
+        }
+        if (!__any_sync(PATHS_FULL_MASK, has)) break;
+#pragma unroll 1
+        for (int r = 0; r < ROUNDS; r++) {
+            if (has) {
+#pragma unroll 1
+                for (int k = 0; k < KI && tv.node >= 0; k++) tv.inner4(nodes4, sstack, stride);
+                if (tv.node < 0 && tv.node != PATHS_TRAV_DONE) {
+                    tv.leaf_test<false>(leaves, tv.node, 0xFFFFFFFFu);
+                    tv.node = tv.pop4(sstack, stride);
+                }
+                if (tv.node == PATHS_TRAV_DONE) {
+                    ps.hit[slot] = make_float4(__uint_as_float(tv.prim), tv.t, tv.bx, tv.by);
+                    has = false;
+                }
+            }
+        }
+    }
+}
+
+template <int ROUNDS, int MIN_REFILL, int KI>
+__global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_shadow4(DevScene sc, PathState<float4> ps, const uint32_t *count_ptr, uint32_t *cursor,
+                                                                  unsigned long long *totals) {
+    extern __shared__ int32_t smem_stack[];
+    int32_t *sstack = smem_stack + threadIdx.x;
+    const uint32_t stride = blockDim.x;
+    const uint32_t count = *count_ptr;
+    const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    const float4 *__restrict__ nodes4 = sc.fast4_nodes;
+    const float4 *__restrict__ leaves = sc.fast_leaves;
+    TravF4 tv;
+    tv.node = PATHS_TRAV_DONE;
+    bool has = false, exhausted = false;
+    uint32_t rec = 0, slot = 0, skip = 0xFFFFFFFFu;
+    for (;;) {
+        unsigned idle = __ballot_sync(PATHS_FULL_MASK, !has);
+        int n = __popc(idle);
+        if (!exhausted && n >= MIN_REFILL) {
+            int leader = __ffs(idle) - 1;
+            uint32_t base = 0;
+            if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)n);
+            base = __shfl_sync(PATHS_FULL_MASK, base, leader);
+            if (!has) {
+                uint32_t i = base + __popc(idle & lt);
+                if (i < count) {
+                    rec = i;
+                    float4 o = ps.sh_o[i], d = ps.sh_d[i];
+                    uint32_t lid = __float_as_uint(o.w);
+                    slot = __float_as_uint(d.w);
+                    const DevLight &l = sc.lights[lid];
+                    float t_light = __int_as_float(0x7f800000);
+                    if (l.geometry == 1) {
+                        double tl;
+                        if (sphere_hit64(mk3(l.v[0], l.v[1], l.v[2]), l.radius, mk3((double)o.x, (double)o.y, (double)o.z),
+                                         mk3((double)d.x, (double)d.y, (double)d.z), tl))
+                            t_light = (float)tl;
+                    }
+                    skip = l.prim;
+                    tv.init(o.x, o.y, o.z, d.x, d.y, d.z, t_light, sc.fast4_root);
+                    has = true;
+                }
+            }
+            exhausted = base + (uint32_t)n >= count;
+        }
+        if (!__any_sync(PATHS_FULL_MASK, has)) break;
+#pragma unroll 1
+        for (int r = 0; r < ROUNDS; r++) {
+            if (has) {
+#pragma unroll 1
+                for (int k = 0; k < KI && tv.node >= 0; k++) tv.inner4(nodes4, sstack, stride);
+                bool occluded = false;
+                if (tv.node < 0 && tv.node != PATHS_TRAV_DONE) {
+                    occluded = tv.leaf_test<true>(leaves, tv.node, skip);
+                    tv.node = tv.pop4(sstack, stride);
+                }
+                if (occluded) has = false;
+                else if (tv.node == PATHS_TRAV_DONE) {
+                    float4 c = ps.sh_c[rec];
+                    float4 col = ps.col[slot];
+                    col.x += c.x; col.y += c.y; col.z += c.z;
+                    if (col.x < 0.0f || col.y < 0.0f || col.z < 0.0f) atomicAdd(totals + 2, 1ull);
+                    ps.col[slot] = col;
+                    has = false;
+                }
+            }
+        }
+    }
+}
+
 // ------------------------------------------------------------------ accumulate (src/pixels.rs:6-31,49-51; worker.rs:76 applies the camera weight)
 template <typename R>
 __global__ void __launch_bounds__(256) k_accumulate(PathState<typename Vec4T<R>::type> ps, ShardInfo shard, uint32_t spp_pass,

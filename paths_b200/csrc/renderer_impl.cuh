@@ -16,7 +16,8 @@ template <typename R> class RendererImpl : public RendererBase {
     uint32_t W_, H_, npix_, n_local_ = 0, spp_pass_ = 1, n_ctl_ = 0;
     size_t n_slots_max_ = 0;
     uint32_t samples_done_ = 0; // global samples per pixel issued so far (all ranks together)
-    int sm_count_ = 148, grid_trace_ = 0, grid_shade_ = 0, grid_stream_ = 0, variant_ = 3;
+    int sm_count_ = 148, grid_trace_ = 0, grid_shade_ = 0, grid_stream_ = 0, variant_ = 3, grid4_ = 0;
+    size_t smem4_ = 0;
     // device buffers
     R4 *sums_ = nullptr;
     uint32_t *pixels_ = nullptr; // tile shard: local -> global pixel
@@ -159,6 +160,9 @@ template <typename R> class RendererImpl : public RendererBase {
         pc_.work = ctl_block_ + 2 * nb;
         if (alloc(&pc_.totals, 4) != PATHS_OK) return PATHS_ERR_CUDA;
         PATHS_CU(cudaMemset(pc_.totals, 0, 4 * sizeof(unsigned long long)));
+        // traversal kernel: two-wide nodes + local stack for small (L1-resident) scenes, four-wide nodes + shared-memory stack
+        // above 64k primitives (measured: teapot 7.5 vs 7.8 ms, dragon 25.4 vs 24.4 ms per 16 spp; profiles/r01_*)
+        variant_ = sd_->view.n_prims > 65536u ? 12 : 3;
         if (const char *v = getenv("PATHS_EXTEND_VARIANT")) variant_ = atoi(v); // development switch between traversal kernels
         // ---- persistent grids: every SM full
         int bps = 0;
@@ -168,6 +172,20 @@ template <typename R> class RendererImpl : public RendererBase {
         PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_shade<R>, 128, 0));
         grid_shade_ = sm_count_ * std::max(bps, 1);
         grid_stream_ = sm_count_ * 8;
+        if constexpr (!IsF64<R>::value) {
+            // four-wide kernels: stack of 3 * depth + 1 levels per thread in shared memory
+            smem4_ = (size_t)(3 * sd_->view.fast4_depth + 1) * 128 * sizeof(int32_t);
+            if (smem4_ > 200 * 1024) {
+                if (variant_ >= 10) variant_ = 3; // pathological tree: the two-wide kernels keep their stack in local memory
+            } else {
+                PATHS_CU(cudaFuncSetAttribute(k_extend4<4, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
+                PATHS_CU(cudaFuncSetAttribute(k_extend4<4, 16, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
+                PATHS_CU(cudaFuncSetAttribute(k_extend4<2, 16, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
+                PATHS_CU(cudaFuncSetAttribute(k_shadow4<4, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
+                PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_extend4<4, 16, 2>, 128, smem4_));
+                grid4_ = sm_count_ * std::max(bps, 1);
+            }
+        }
         return PATHS_OK;
     }
 
@@ -185,6 +203,9 @@ template <typename R> class RendererImpl : public RendererBase {
             case 7: k_extend_spec<4, 16, 4><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
             case 8: k_extend_spec<2, 16, 6><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
             case 9: k_extend_spec<4, 8, 2><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 10: k_extend4<4, 16, 2><<<grid4_, 128, smem4_, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 11: k_extend4<4, 16, 1><<<grid4_, 128, smem4_, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 12: k_extend4<2, 16, 3><<<grid4_, 128, smem4_, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
             default: break;
             }
         }
@@ -192,6 +213,10 @@ template <typename R> class RendererImpl : public RendererBase {
     }
     void launch_shadow(uint32_t b) {
         if constexpr (!IsF64<R>::value) {
+            if (variant_ >= 10) {
+                k_shadow4<4, 16, 2><<<grid4_, 128, smem4_, stream_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
+                return;
+            }
             if (variant_ != 0) {
                 k_shadow_refill<4, 8><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
                 return;

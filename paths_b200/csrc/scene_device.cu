@@ -127,6 +127,12 @@ SceneDevice *upload_scene(int device, const HostScene &hs, const RefTree *ref, c
         }
         ok = ok && put(sd, nodes, &v.fast_nodes, err) && put(sd, leaves, &v.fast_leaves, err);
         v.fast_root = fast->root;
+        static_assert(sizeof(FastNode4) == 128, "FastNode4 must be one cache line");
+        std::vector<float4> nodes4(fast->nodes4.size() * 8);
+        if (!fast->nodes4.empty()) std::memcpy(nodes4.data(), fast->nodes4.data(), fast->nodes4.size() * sizeof(FastNode4));
+        ok = ok && put(sd, nodes4, &v.fast4_nodes, err);
+        v.fast4_root = fast->root4;
+        v.fast4_depth = fast->depth4;
     }
     if (ok) { // shading tables
         std::vector<DevObject> objs(hs.objects.size());
