@@ -123,6 +123,15 @@ typedef struct paths_renderer paths_renderer;
 enum { PATHS_PRECISION_AUTO = 0, PATHS_PRECISION_F32 = 32, PATHS_PRECISION_F64 = 64 };
 enum { PATHS_SHARD_SAMPLES = 0, PATHS_SHARD_TILES = 1 };
 enum { PATHS_BVH_FAST = 0, PATHS_BVH_REFERENCE = 1 };
+/* Estimator extensions that have NO reference behaviour; all off by default so that output stays in parity.
+ *   ENV_NEE        next-event estimation toward an Hdri sky through a CDF table (the reference only looks the map up on a miss,
+ *                  src/scene.rs:95-111); a sky miss then counts only after a specular bounce, like light hits do (trace.rs:31-41)
+ *   MICROFACET     importance-sample CookTorrance (Beckmann half vectors) and Fresnel combinations instead of ending the path
+ *                  where Material::sample panics (src/material.rs:86)
+ *   MICROFACET_COSINE  same materials sampled with a plain cosine lobe (cross-check of the estimator above)
+ *   GGX            evaluate and sample CookTorrance with the GGX distribution instead of Beckmann (src/material.rs:436-447)
+ *   NEE_ALL_LIGHTS weight the one-light NEE sample by the number of lights (the reference omits the factor, scene.rs:199-206) */
+enum { PATHS_EXT_ENV_NEE = 1, PATHS_EXT_MICROFACET = 2, PATHS_EXT_MICROFACET_COSINE = 4, PATHS_EXT_GGX = 8, PATHS_EXT_NEE_ALL_LIGHTS = 16 };
 
 typedef struct {
     int32_t device;        /* CUDA ordinal */
@@ -133,7 +142,7 @@ typedef struct {
     uint32_t max_bounces;  /* trace.rs:14 (10) */
     uint32_t samples_per_pass; /* camera samples per pixel kept in flight per wavefront pass; 0 = choose */
     int32_t time_kernels;  /* record CUDA events around every kernel (paths_stats.ms_*) */
-    int32_t _pad;
+    uint32_t extensions;   /* PATHS_EXT_* bit mask, 0 = the reference's estimator */
 } paths_render_opts;
 
 typedef struct {

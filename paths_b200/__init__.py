@@ -11,7 +11,7 @@ import ctypes as C
 import numpy as np
 
 from . import _capi
-from ._capi import (MISS, PRECISION_AUTO, PRECISION_F32, PRECISION_F64, SHARD_SAMPLES, SHARD_TILES, Camera, PathsError,  # noqa: F401
+from ._capi import (EXT_ENV_NEE, EXT_GGX, EXT_MICROFACET, EXT_MICROFACET_COSINE, EXT_NEE_ALL_LIGHTS, MISS, PRECISION_AUTO, PRECISION_F32, PRECISION_F64, SHARD_SAMPLES, SHARD_TILES, Camera, PathsError,  # noqa: F401
                     RenderOpts, SceneInfo, Stats, build, check, lib)
 
 __all__ = ["Scene", "Renderer", "Image", "Camera", "PathsError", "build", "lib", "camera_rays", "device_count", "MISS"]
@@ -195,7 +195,7 @@ class Renderer:
     """
 
     def __init__(self, camera, scene, device=0, precision=PRECISION_AUTO, seed=1, rank=0, world=1, shard_mode=SHARD_SAMPLES,
-                 max_bounces=10, samples_per_pass=0, time_kernels=False):
+                 max_bounces=10, samples_per_pass=0, time_kernels=False, extensions=0):
         self._h = None
         self.scene = scene
         self.camera = camera if isinstance(camera, Camera) else camera_from_dict(camera)
@@ -203,6 +203,7 @@ class Renderer:
         lib().paths_render_opts_default(C.byref(o))
         o.device, o.precision, o.seed, o.rank, o.world, o.shard_mode = device, precision, seed, rank, world, shard_mode
         o.max_bounces, o.samples_per_pass, o.time_kernels = max_bounces, samples_per_pass, 1 if time_kernels else 0
+        o.extensions = extensions
         h = C.c_void_p()
         check(lib().paths_renderer_create(scene._h, C.byref(self.camera), C.byref(o), C.byref(h)))
         self._h = h

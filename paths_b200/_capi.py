@@ -16,6 +16,7 @@ OK, ERR_INVALID_ARG, ERR_IO, ERR_PARSE, ERR_CUDA, ERR_UNSUPPORTED, ERR_INTERNAL 
 MISS = 0xFFFFFFFF
 PRECISION_AUTO, PRECISION_F32, PRECISION_F64 = 0, 32, 64
 SHARD_SAMPLES, SHARD_TILES = 0, 1
+EXT_ENV_NEE, EXT_MICROFACET, EXT_MICROFACET_COSINE, EXT_GGX, EXT_NEE_ALL_LIGHTS = 1, 2, 4, 8, 16
 MAT_TYPES = {"Lambertian": 0, "Mirror": 1, "Gloss": 2, "CookTorrance": 3, "Fresnel": 4}
 
 
@@ -71,7 +72,7 @@ class Camera(C.Structure):
 class RenderOpts(C.Structure):
     _fields_ = [("device", C.c_int32), ("precision", C.c_int32), ("shard_mode", C.c_int32), ("rank", C.c_uint32), ("world", C.c_uint32),
                 ("seed", C.c_uint64), ("max_bounces", C.c_uint32), ("samples_per_pass", C.c_uint32), ("time_kernels", C.c_int32),
-                ("_pad", C.c_int32)]
+                ("extensions", C.c_uint32)]
 
 
 class Stats(C.Structure):

@@ -12,6 +12,7 @@ namespace paths {
 
 #define PATHS_TAG_PATH 0x50415448u /* 'PATH' */
 #define PATHS_TAG_CMJ 0x434D4A20u  /* 'CMJ ' */
+#define PATHS_TAG_ENV 0x454E5620u  /* 'ENV ' : environment NEE samples (extension) */
 
 struct U4 {
     uint32_t v[4];

@@ -9,6 +9,7 @@ namespace paths {
 //   x: bit0 = triangle, bit1 = entity is a light;  y: entity id;  z: face index in its model;  w: unused
 #define PATHS_PM_TRI 1u
 #define PATHS_PM_LIGHT 2u
+#define PATHS_LIGHT_ENV 0xFFFFFFFEu /* shadow-record light id of an environment NEE sample */
 
 struct DevObject {          // src/scene.rs:35-40 + src/geom.rs:98-122 + resolved material record
     int32_t shape, smooth;
@@ -66,6 +67,8 @@ struct DevScene {
     double sky_c0[3], sky_c1[3];
     uint32_t sky_w, sky_h;
     const float *sky_texels;
+    const float *env_marginal;    // [sky_h + 1]
+    const float *env_conditional; // [sky_h][sky_w + 1]
 };
 
 struct DevCamera { // src/camera.rs:12-27 after CameraDescription::to_camera (src/serde.rs:172-188)

@@ -45,6 +45,7 @@ template <typename R> struct MatR {
     int type;
     V3<R> albedo;
     R r0, metalness, roughness;
+    bool ggx; // extension PATHS_EXT_GGX: CookTorrance evaluated with the GGX distribution instead of Beckmann
 };
 
 template <typename R> __device__ __forceinline__ V3<R> reflect(V3<R> vector, V3<R> normal) { // :249-251
@@ -74,6 +75,13 @@ template <typename R> __device__ __forceinline__ R beckmann_ndf(R m, V3<R> n, V3
     R d0 = e / (Consts<R>::pi() * m * m * pow_(cos_alpha, R(4.0)));
     return fmax_(R(0.0), d0 * dot(n, h));
 }
+// extension: the GGX / Trowbridge-Reitz distribution in the same D * (n.h) form as ct_ndf above
+template <typename R> __device__ __forceinline__ R ggx_ndf(R m, V3<R> n, V3<R> h) {
+    R c = dot(n, h);
+    R a2 = m * m;
+    R q = c * c * (a2 - R(1.0)) + R(1.0);
+    return fmax_(R(0.0), a2 / (Consts<R>::pi() * q * q) * c);
+}
 template <typename R> __device__ __forceinline__ V3<R> basic_brdf(const MatR<R> &b, V3<R> vec_out, V3<R> vec_in, V3<R> normal) {
     const V3<R> black = mk3<R>(R(0), R(0), R(0));
     if (b.type == 0) return lambert_brdf(b.albedo, vec_in, normal);
@@ -84,7 +92,7 @@ template <typename R> __device__ __forceinline__ V3<R> basic_brdf(const MatR<R> 
     }
     if (b.type == 3) { // :503-523
         V3<R> h = normed(vec_out - vec_in);
-        R d = beckmann_ndf(b.roughness, normal, h);
+        R d = b.ggx ? ggx_ndf(b.roughness, normal, h) : beckmann_ndf(b.roughness, normal, h);
         R ndl = dot(normal, neg(vec_in));
         R vdh = dot(vec_out, h);
         R ndh = dot(normal, h);
@@ -109,6 +117,7 @@ template <typename R> __device__ __forceinline__ Material<R> load_material(const
     mt.m.r0 = R(o.r0);
     mt.m.metalness = R(o.metalness);
     mt.m.roughness = R(o.roughness);
+    mt.m.ggx = mt.diffuse.ggx = mt.specular.ggx = false;
     mt.fresnel = o.mat_type == 4;
     if (mt.fresnel) {
         mt.fresnel_r0 = R(o.fresnel_r0);
@@ -170,6 +179,104 @@ template <typename R> __device__ __forceinline__ bool material_sample(const Mate
         return true;
     }
     return false;
+}
+
+// ------------------------------------------------------------------ extensions without reference behaviour (PATHS_EXT_*)
+// Microfacet sampling.  The reference evaluates CookTorrance / Fresnel combinations (brdf(), material.rs:414-421,503-523) but its
+// Material::sample panics for them (material.rs:81-88).  Here: sample a Beckmann (or GGX) half vector h with density D(h)(n.h),
+// reflect vec_out about it, pdf(dir) = D(h)(n.h) / (4 vec_out.h); the weight is the REFERENCE's brdf() over that pdf, so the
+// estimator integrates exactly the function the reference's NEE term uses.
+template <typename R> __device__ __forceinline__ bool cook_torrance_sample(const MatR<R> &b, V3<R> vec_out, V3<R> normal, R u1, R u2, bool cosine,
+                                                                            V3<R> &direction, R &pdf, V3<R> &brdf) {
+    R sn, cs;
+    sincos_2pi(u2, &sn, &cs);
+    if (cosine) { // plain cosine lobe (cross-check estimator)
+        R r = sqrt_(u1), y = sqrt_(fmax_(R(0.0), R(1.0) - u1));
+        direction = normed(to_world(mk3<R>(r * cs, y, r * sn), normal));
+        pdf = dot(normal, direction) / Consts<R>::pi();
+    } else {
+        R m = b.roughness;
+        R tan2 = b.ggx ? m * m * u1 / fmax_(R(1e-12), R(1.0) - u1) : -m * m * log(fmax_(R(1e-30), R(1.0) - u1));
+        R cos_t = R(1.0) / sqrt_(R(1.0) + tan2);
+        R sin_t = sqrt_(fmax_(R(0.0), R(1.0) - cos_t * cos_t));
+        V3<R> h = normed(to_world(mk3<R>(sin_t * cs, cos_t, sin_t * sn), normal));
+        R vdh = dot(vec_out, h);
+        if (!(vdh > R(0))) return false;
+        direction = normed(h * (R(2.0) * vdh) - vec_out);
+        R d = b.ggx ? ggx_ndf(m, normal, h) : beckmann_ndf(m, normal, h);
+        pdf = d / (R(4.0) * vdh);
+    }
+    if (!(dot(normal, direction) > R(0)) || !(pdf > R(0))) return false;
+    brdf = basic_brdf(b, vec_out, neg(direction), normal);
+    return true;
+}
+
+template <typename R> __device__ __forceinline__ bool basic_sample_ext(const MatR<R> &b, V3<R> vec_out, V3<R> normal, R u0, R u1, R u2, bool cosine,
+                                                                        V3<R> &direction, R &pdf, V3<R> &brdf, bool &is_specular) {
+    if (b.type == 3) {
+        is_specular = false;
+        return cook_torrance_sample(b, vec_out, normal, u1, u2, cosine, direction, pdf, brdf);
+    }
+    Material<R> tmp;
+    tmp.m = b;
+    tmp.fresnel = false;
+    return material_sample<R>(tmp, vec_out, normal, u0, u1, u2, direction, pdf, brdf, is_specular);
+}
+
+// us = {branch choice, gloss choice, hemisphere / half-vector u, v}
+template <typename R> __device__ __forceinline__ bool material_sample_ext(const Material<R> &mt, V3<R> vec_out, V3<R> normal, R uc, R u0, R u1, R u2,
+                                                                           bool cosine, V3<R> &direction, R &pdf, V3<R> &brdf, bool &is_specular) {
+    if (!mt.fresnel) return basic_sample_ext(mt.m, vec_out, normal, u0, u1, u2, cosine, direction, pdf, brdf, is_specular);
+    // one-sample estimator of r f_s + (1 - r) f_d (material.rs:414-421): pick a lobe with probability ps, divide by it
+    R r = schlick(mt.fresnel_r0, vec_out, normal);
+    R ps = fmin_(R(0.9), fmax_(R(0.1), r));
+    if (uc < ps) {
+        if (!basic_sample_ext(mt.specular, vec_out, normal, u0, u1, u2, cosine, direction, pdf, brdf, is_specular)) return false;
+        brdf = brdf * r;
+        pdf = pdf * ps;
+    } else {
+        if (!basic_sample_ext(mt.diffuse, vec_out, normal, u0, u1, u2, cosine, direction, pdf, brdf, is_specular)) return false;
+        brdf = brdf * (R(1.0) - r);
+        pdf = pdf * (R(1.0) - ps);
+    }
+    return true;
+}
+
+// Environment importance sampling: picks a texel of the Hdri sky with probability proportional to luminance x solid angle
+// (tables built by host_scene.cpp), a uniform point inside it, and returns the LOOKUP direction (what Skybox::ambient_light is
+// called with, scene.rs:95-111), its solid-angle density and the texel radiance.
+template <typename R> __device__ __forceinline__ void env_sample(const DevScene &sc, R u1, R u2, V3<R> &lookup_dir, R &pdf, V3<R> &radiance) {
+    const uint32_t w = sc.sky_w, h = sc.sky_h;
+    uint32_t lo = 0, hi = h;
+    while (lo < hi) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (sc.env_marginal[mid + 1] <= (float)u1) lo = mid + 1;
+        else hi = mid;
+    }
+    uint32_t y = min(lo, h - 1);
+    float m0 = sc.env_marginal[y], m1 = sc.env_marginal[y + 1];
+    R fy = fmin_(R(0.999999), fmax_(R(0.0), (u1 - R(m0)) / fmax_(R(1e-20), R(m1 - m0))));
+    const float *cond = sc.env_conditional + (size_t)y * (w + 1);
+    lo = 0;
+    hi = w;
+    while (lo < hi) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (cond[mid + 1] <= (float)u2) lo = mid + 1;
+        else hi = mid;
+    }
+    uint32_t x = min(lo, w - 1);
+    float c0 = cond[x], c1 = cond[x + 1];
+    R fx = fmin_(R(0.999999), fmax_(R(0.0), (u2 - R(c0)) / fmax_(R(1e-20), R(c1 - c0))));
+    R lat = Consts<R>::pi() * (R(1.0) - (R(y) + fy) / R(h));
+    R lon = Consts<R>::pi() * (R(2.0) * (R(x) + fx) / R(w) - R(1.0));
+    R sl, cl, so, co;
+    sincos_(lat, &sl, &cl);
+    sincos_(lon, &so, &co);
+    lookup_dir = mk3<R>(sl * co, cl, sl * so);
+    R prob = R(m1 - m0) * R(c1 - c0);
+    pdf = prob * R(w) * R(h) / (R(2.0) * Consts<R>::pi() * Consts<R>::pi() * fmax_(R(1e-12), sl));
+    size_t pix = (size_t)y * w + x;
+    radiance = mk3<R>(R(sc.sky_texels[3 * pix]), R(sc.sky_texels[3 * pix + 1]), R(sc.sky_texels[3 * pix + 2]));
 }
 
 // ------------------------------------------------------------------ lights (src/scene.rs:54-59, src/geom.rs:146-173)

@@ -228,6 +228,34 @@ bool build_host_scene(const paths_scene_desc &desc, HostScene &out, std::string 
         out.sky_w = desc.sky.width;
         out.sky_h = desc.sky.height;
         out.sky_texels.assign(desc.sky.texels, desc.sky.texels + (size_t)3 * desc.sky.width * desc.sky.height);
+        // piecewise-constant importance function: texel luminance x solid angle (row y covers latitude pi (1 - (y + .5) / h),
+        // the mapping of src/scene.rs:95-111)
+        const uint32_t w = out.sky_w, h = out.sky_h;
+        out.env_marginal.assign((size_t)h + 1, 0.0f);
+        out.env_conditional.assign((size_t)h * (w + 1), 0.0f);
+        std::vector<double> row_sum(h, 0.0);
+        const double pi = 3.14159265358979323846;
+        for (uint32_t y = 0; y < h; y++) {
+            double sin_lat = std::sin(pi * (1.0 - (y + 0.5) / h));
+            double acc = 0.0;
+            float *cond = &out.env_conditional[(size_t)y * (w + 1)];
+            for (uint32_t x = 0; x < w; x++) {
+                const float *t = &out.sky_texels[3 * ((size_t)y * w + x)];
+                double lum = std::fmax(0.0, ((double)t[0] + t[1] + t[2]) / 3.0) + 1e-12;
+                acc += lum;
+                cond[x + 1] = (float)acc;
+            }
+            for (uint32_t x = 1; x <= w; x++) cond[x] = (float)(cond[x] / acc);
+            cond[w] = 1.0f;
+            row_sum[y] = acc * sin_lat;
+        }
+        double tot = 0.0;
+        for (uint32_t y = 0; y < h; y++) {
+            tot += row_sum[y];
+            out.env_marginal[y + 1] = (float)tot;
+        }
+        for (uint32_t y = 1; y <= h; y++) out.env_marginal[y] = (float)(out.env_marginal[y] / tot);
+        out.env_marginal[h] = 1.0f;
     } else if (desc.sky.type != 0 && desc.sky.type != 1) {
         err = "unknown skybox type";
         return false;

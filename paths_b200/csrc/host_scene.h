@@ -131,6 +131,8 @@ struct HostScene {
     double sky_c0[3], sky_c1[3];
     uint32_t sky_w = 0, sky_h = 0;
     std::vector<float> sky_texels;
+    // importance tables of the Hdri sky (extension ENV_NEE): row marginal CDF [h + 1], per-row conditional CDFs [h][w + 1]
+    std::vector<float> env_marginal, env_conditional;
     uint32_t n_tris = 0, n_spheres = 0, hidden = 0;
     D3 bounds_lo, bounds_hi;
     int auto_precision = 32;

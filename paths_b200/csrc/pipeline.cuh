@@ -6,6 +6,7 @@
 // queues with one ballot + popc + atomicAdd per warp.  All kernels are persistent: a fixed grid of warps pulls
 // batches of 32 queue entries through an atomic cursor, so no host round trip is needed to learn queue lengths.
 #pragma once
+#include "../../include/paths_b200.h"
 #include "dev_shade.cuh"
 #include "dev_trace.cuh"
 
@@ -93,14 +94,14 @@ __global__ void __launch_bounds__(128) k_extend(DevScene sc, PathState<typename 
 
 // ------------------------------------------------------------------ shade: one iteration of trace_ray's loop body (src/trace.rs:13-118)
 template <typename R> struct ShadeOut {
-    bool alive, shadow;
-    V3<R> sh_o, sh_d, sh_c;
+    bool alive, shadow, shadow2; // shadow2: environment NEE sample (extension)
+    V3<R> sh_o, sh_d, sh_c, sh2_d, sh2_c;
     uint32_t light;
 };
 
 template <typename R>
 __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typename Vec4T<R>::type> &ps, uint32_t slot, uint32_t pixel, uint32_t S,
-                                           uint32_t k0, uint32_t k1, uint32_t max_bounces, unsigned long long *totals, ShadeOut<R> &out) {
+                                           uint32_t k0, uint32_t k1, uint32_t max_bounces, uint32_t ext, unsigned long long *totals, ShadeOut<R> &out) {
     typedef typename Vec4T<R>::type R4;
     const V3<R> black = mk3<R>(R(0), R(0), R(0));
     R4 o4 = ps.ray_o[slot], d4 = ps.ray_d[slot], h4 = ps.hit[slot], t4 = ps.thr[slot];
@@ -112,8 +113,13 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
     uint32_t prim = real_to_bits(h4.x);
     out.alive = false;
     out.shadow = false;
+    out.shadow2 = false;
+    const bool env_nee = (ext & PATHS_EXT_ENV_NEE) && sc.sky_type == 2;
 
     if (prim == 0xFFFFFFFFu) { // trace.rs:20-23
+        // with environment NEE the sky is accounted for at the previous vertex unless that bounce was specular (same rule
+        // the reference applies to lights, trace.rs:31-41)
+        if (env_nee && !last_specular) return;
         R4 c4 = ps.col[slot]; // the radiance record is only touched by the branches that add light
         V3<R> colour = mk3<R>(c4.x, c4.y, c4.z);
         colour = colour + throughput * sky_light<R>(sc, neg(rd));
@@ -164,6 +170,8 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
     }
     // ---- material resolve (trace.rs:44-50, material.rs:39-49,183-195, model.rs:158-172)
     Material<R> mat = load_material<R>(*obj);
+    mat.m.ggx = mat.diffuse.ggx = mat.specular.ggx = (ext & PATHS_EXT_GGX) != 0;
+    const bool micro = (ext & (PATHS_EXT_MICROFACET | PATHS_EXT_MICROFACET_COSINE)) != 0 && (mat.fresnel || mat.m.type == 3);
     if (face && !mat.fresnel && (mat.m.type == 0 || mat.m.type == 2) && obj->vertex_albedo) {
         const double *vc = sc.vertex_colours + 3 * (size_t)obj->vert_base;
         V3<R> ac = mk3<R>(R(vc[3 * face[0]]), R(vc[3 * face[0] + 1]), R(vc[3 * face[0] + 2]));
@@ -175,8 +183,8 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
     U4 r0, r1;
     r0.v[0] = r0.v[1] = r0.v[2] = r0.v[3] = 0u;
     r1 = r0;
-    if (sc.n_lights > 0 || mat.m.type == 2) r0 = philox4x32_10(pixel, S, loops * 2u, PATHS_TAG_PATH, k0, k1);
-    if (loops >= 2 || mat.m.type == 0 || mat.m.type == 2) r1 = philox4x32_10(pixel, S, loops * 2u + 1u, PATHS_TAG_PATH, k0, k1);
+    if (sc.n_lights > 0 || mat.m.type == 2 || micro) r0 = philox4x32_10(pixel, S, loops * 2u, PATHS_TAG_PATH, k0, k1);
+    if (loops >= 2 || mat.m.type == 0 || mat.m.type == 2 || micro) r1 = philox4x32_10(pixel, S, loops * 2u + 1u, PATHS_TAG_PATH, k0, k1);
     V3<R> vec_out = neg(rd);
     V3<R> new_origin = location + normal * R(0.0001); // trace.rs:57,89
 
@@ -194,6 +202,7 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
             V3<R> base = mk3<R>(R(light.colour[0]), R(light.colour[1]), R(light.colour[2])) * R(light.intensity);
             V3<R> brdf = material_brdf<R>(mat, vec_out, neg(sdir), normal);
             V3<R> direct = base * brdf * inv_pdf;
+            if (ext & PATHS_EXT_NEE_ALL_LIGHTS) direct = direct * R(nl); // extension: undo the uniform light choice
             if (col_bad(direct)) atomicAdd(totals + 2, 1ull); // Colour::check (trace.rs:80)
             V3<R> contrib = direct * throughput;
             // a zero contribution cannot change the estimate: skip its visibility query
@@ -206,11 +215,33 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
             }
         }
     }
+    // ---- extension: one NEE sample toward the Hdri sky, drawn from its CDF table
+    if (env_nee) {
+        U4 r2 = philox4x32_10(pixel, S, loops, PATHS_TAG_ENV, k0, k1);
+        V3<R> lookup, radiance;
+        R epdf;
+        env_sample<R>(sc, u01<R>(r2.v[0]), u01<R>(r2.v[1]), lookup, epdf, radiance);
+        V3<R> sdir = neg(lookup); // a ray leaving along sdir sees ambient_light(-sdir) (trace.rs:21)
+        if (dot(normal, sdir) > R(0) && epdf > R(0)) {
+            V3<R> f = material_brdf<R>(mat, vec_out, lookup, normal); // vec_in = direction the light travels = -sdir
+            V3<R> contrib = radiance * f * throughput / epdf;
+            if (contrib.x != R(0) || contrib.y != R(0) || contrib.z != R(0)) {
+                out.shadow2 = true;
+                out.sh_o = new_origin;
+                out.sh2_d = sdir;
+                out.sh2_c = contrib;
+            }
+        }
+    }
     // ---- BSDF sampling (trace.rs:84-98)
     V3<R> direction, brdf;
     R pdf;
     bool is_specular;
-    if (!material_sample<R>(mat, vec_out, normal, u01<R>(r0.v[3]), u01<R>(r1.v[0]), u01<R>(r1.v[1]), direction, pdf, brdf, is_specular)) {
+    if (micro) {
+        if (!material_sample_ext<R>(mat, vec_out, normal, u01<R>(r0.v[0]), u01<R>(r0.v[3]), u01<R>(r1.v[0]), u01<R>(r1.v[1]),
+                                    (ext & PATHS_EXT_MICROFACET_COSINE) != 0, direction, pdf, brdf, is_specular))
+            return; // sampled below the horizon: zero weight
+    } else if (!material_sample<R>(mat, vec_out, normal, u01<R>(r0.v[3]), u01<R>(r1.v[0]), u01<R>(r1.v[1]), direction, pdf, brdf, is_specular)) {
         atomicAdd(totals + 2, 1ull); // the reference panics: "Not implemented" (material.rs:86)
         return;
     }
@@ -233,8 +264,8 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
 }
 
 template <typename R>
-__global__ void __launch_bounds__(128, PATHS_LB_SHADE) k_shade(DevScene sc, PathState<typename Vec4T<R>::type> ps, ShardInfo shard, uint32_t s_base, uint32_t k0,
-                                               uint32_t k1, uint32_t max_bounces, const uint32_t *queue, uint32_t *queue_next,
+__global__ void __launch_bounds__(128, (IsF64<R>::value ? 2 : PATHS_LB_SHADE)) k_shade(DevScene sc, PathState<typename Vec4T<R>::type> ps, ShardInfo shard, uint32_t s_base, uint32_t k0,
+                                               uint32_t k1, uint32_t max_bounces, uint32_t ext, const uint32_t *queue, uint32_t *queue_next,
                                                const uint32_t *count_ptr, uint32_t *next_count, uint32_t *shadow_count, uint32_t *cursor,
                                                unsigned long long *totals) {
     const uint32_t count = *count_ptr;
@@ -244,19 +275,27 @@ __global__ void __launch_bounds__(128, PATHS_LB_SHADE) k_shade(DevScene sc, Path
         if (base >= count) break;
         uint32_t i = base + lane;
         ShadeOut<R> out;
-        out.alive = out.shadow = false;
+        out.alive = out.shadow = out.shadow2 = false;
         uint32_t slot = 0;
         if (i < count) {
             slot = queue ? queue[i] : i;
             uint32_t lp = slot % shard.n_local, k = slot / shard.n_local;
             uint32_t pixel = shard.pixels ? shard.pixels[lp] : lp;
-            shade_path<R>(sc, ps, slot, pixel, s_base + k, k0, k1, max_bounces, totals, out);
+            shade_path<R>(sc, ps, slot, pixel, s_base + k, k0, k1, max_bounces, ext, totals, out);
         }
         uint32_t spos = warp_append(shadow_count, out.shadow);
         if (out.shadow) {
             ps.sh_o[spos] = mk4(out.sh_o.x, out.sh_o.y, out.sh_o.z, bits_to_real(out.light, R(0)));
             ps.sh_d[spos] = mk4(out.sh_d.x, out.sh_d.y, out.sh_d.z, bits_to_real(slot, R(0)));
             ps.sh_c[spos] = mk4(out.sh_c.x, out.sh_c.y, out.sh_c.z, R(0));
+        }
+        if (ext & PATHS_EXT_ENV_NEE) { // warp-uniform
+            uint32_t epos = warp_append(shadow_count, out.shadow2);
+            if (out.shadow2) {
+                ps.sh_o[epos] = mk4(out.sh_o.x, out.sh_o.y, out.sh_o.z, bits_to_real(PATHS_LIGHT_ENV, R(0)));
+                ps.sh_d[epos] = mk4(out.sh2_d.x, out.sh2_d.y, out.sh2_d.z, bits_to_real(slot, R(0)));
+                ps.sh_c[epos] = mk4(out.sh2_c.x, out.sh2_c.y, out.sh2_c.z, R(0));
+            }
         }
         uint32_t qpos = warp_append(next_count, out.alive);
         if (out.alive) queue_next[qpos] = slot;
@@ -284,20 +323,24 @@ __global__ void __launch_bounds__(128) k_shadow(DevScene sc, PathState<typename 
                 occluded = false;
                 if (h.prim != 0xFFFFFFFFu) {
                     uint4 m = sc.prim_meta[h.prim];
-                    occluded = !((m.x & PATHS_PM_LIGHT) && m.y == lid);
+                    occluded = lid == PATHS_LIGHT_ENV || !((m.x & PATHS_PM_LIGHT) && m.y == lid);
                 }
             } else {
                 // same predicate as an any-hit query: occluded <=> some primitive of another entity lies closer than the
                 // nearest hit on the light's own sphere (t_light = inf for point lights, which own no primitive)
-                const DevLight &l = sc.lights[lid];
                 float t_light = __int_as_float(0x7f800000);
-                if (l.geometry == 1) {
-                    double tl;
-                    if (sphere_hit64(mk3(l.v[0], l.v[1], l.v[2]), l.radius, mk3((double)o.x, (double)o.y, (double)o.z),
-                                     mk3((double)d.x, (double)d.y, (double)d.z), tl))
-                        t_light = (float)tl;
+                uint32_t skip = 0xFFFFFFFFu;
+                if (lid != PATHS_LIGHT_ENV) {
+                    const DevLight &l = sc.lights[lid];
+                    skip = l.prim;
+                    if (l.geometry == 1) {
+                        double tl;
+                        if (sphere_hit64(mk3(l.v[0], l.v[1], l.v[2]), l.radius, mk3((double)o.x, (double)o.y, (double)o.z),
+                                         mk3((double)d.x, (double)d.y, (double)d.z), tl))
+                            t_light = (float)tl;
+                    }
                 }
-                HitF h = trace_fast<true>(sc, (float)o.x, (float)o.y, (float)o.z, (float)d.x, (float)d.y, (float)d.z, t_light, l.prim);
+                HitF h = trace_fast<true>(sc, (float)o.x, (float)o.y, (float)o.z, (float)d.x, (float)d.y, (float)d.z, t_light, skip);
                 occluded = h.prim != 0xFFFFFFFFu;
             }
             if (!occluded) { // trace.rs:81: colour += direct * throughput
@@ -451,15 +494,18 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_shadow_refill(DevScene
                     float4 o = ps.sh_o[i], d = ps.sh_d[i];
                     uint32_t lid = __float_as_uint(o.w);
                     slot = __float_as_uint(d.w);
-                    const DevLight &l = sc.lights[lid];
                     float t_light = __int_as_float(0x7f800000);
-                    if (l.geometry == 1) { // nearest hit on the light's own sphere bounds the search (see k_shadow)
-                        double tl;
-                        if (sphere_hit64(mk3(l.v[0], l.v[1], l.v[2]), l.radius, mk3((double)o.x, (double)o.y, (double)o.z),
-                                         mk3((double)d.x, (double)d.y, (double)d.z), tl))
-                            t_light = (float)tl;
+                    skip = 0xFFFFFFFFu;
+                    if (lid != PATHS_LIGHT_ENV) { // nearest hit on the light's own sphere bounds the search (see k_shadow)
+                        const DevLight &l = sc.lights[lid];
+                        skip = l.prim;
+                        if (l.geometry == 1) {
+                            double tl;
+                            if (sphere_hit64(mk3(l.v[0], l.v[1], l.v[2]), l.radius, mk3((double)o.x, (double)o.y, (double)o.z),
+                                             mk3((double)d.x, (double)d.y, (double)d.z), tl))
+                                t_light = (float)tl;
+                        }
                     }
-                    skip = l.prim;
                     tv.init(o.x, o.y, o.z, d.x, d.y, d.z, t_light, sc.fast_root);
                     has = true;
                 }
@@ -570,15 +616,18 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_shadow4(DevScene sc, P
                     float4 o = ps.sh_o[i], d = ps.sh_d[i];
                     uint32_t lid = __float_as_uint(o.w);
                     slot = __float_as_uint(d.w);
-                    const DevLight &l = sc.lights[lid];
                     float t_light = __int_as_float(0x7f800000);
-                    if (l.geometry == 1) {
-                        double tl;
-                        if (sphere_hit64(mk3(l.v[0], l.v[1], l.v[2]), l.radius, mk3((double)o.x, (double)o.y, (double)o.z),
-                                         mk3((double)d.x, (double)d.y, (double)d.z), tl))
-                            t_light = (float)tl;
+                    skip = 0xFFFFFFFFu;
+                    if (lid != PATHS_LIGHT_ENV) { // nearest hit on the light's own sphere bounds the search (see k_shadow)
+                        const DevLight &l = sc.lights[lid];
+                        skip = l.prim;
+                        if (l.geometry == 1) {
+                            double tl;
+                            if (sphere_hit64(mk3(l.v[0], l.v[1], l.v[2]), l.radius, mk3((double)o.x, (double)o.y, (double)o.z),
+                                             mk3((double)d.x, (double)d.y, (double)d.z), tl))
+                                t_light = (float)tl;
+                        }
                     }
-                    skip = l.prim;
                     tv.init(o.x, o.y, o.z, d.x, d.y, d.z, t_light, sc.fast4_root);
                     has = true;
                 }

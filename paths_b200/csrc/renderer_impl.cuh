@@ -148,9 +148,14 @@ template <typename R> class RendererImpl : public RendererBase {
         }
         if (alloc(&sums_, npix_) != PATHS_OK) return PATHS_ERR_CUDA;
         PATHS_CU(cudaMemset(sums_, 0, (size_t)npix_ * sizeof(R4)));
-        R4 **state[] = {&ps_.ray_o, &ps_.ray_d, &ps_.hit, &ps_.thr, &ps_.col, &ps_.sh_o, &ps_.sh_d, &ps_.sh_c};
+        R4 **state[] = {&ps_.ray_o, &ps_.ray_d, &ps_.hit, &ps_.thr, &ps_.col};
         for (R4 **p : state)
             if (alloc(p, n_slots_max_) != PATHS_OK) return PATHS_ERR_CUDA;
+        // shadow records: one per path and bounce for light NEE, one more with environment NEE
+        size_t n_shadow = n_slots_max_ * ((opts_.extensions & PATHS_EXT_ENV_NEE) ? 2 : 1);
+        R4 **shadow[] = {&ps_.sh_o, &ps_.sh_d, &ps_.sh_c};
+        for (R4 **p : shadow)
+            if (alloc(p, n_shadow) != PATHS_OK) return PATHS_ERR_CUDA;
         if (alloc(&pc_.queue[0], n_slots_max_) != PATHS_OK || alloc(&pc_.queue[1], n_slots_max_) != PATHS_OK) return PATHS_ERR_CUDA;
         uint32_t nb = opts_.max_bounces + 2;
         n_ctl_ = 5 * nb;
@@ -244,10 +249,11 @@ template <typename R> class RendererImpl : public RendererBase {
             toc();
             stats_.n_extend_launches++;
             tic(2);
-            k_shade<R><<<grid_shade_, 128, 0, stream_>>>(sd_->view, ps_, shard, s_base, k0, k1, opts_.max_bounces, q, pc_.queue[(b + 1) & 1],
+            k_shade<R><<<grid_shade_, 128, 0, stream_>>>(sd_->view, ps_, shard, s_base, k0, k1, opts_.max_bounces, opts_.extensions, q,
+                                                        pc_.queue[(b + 1) & 1],
                                                         pc_.qcount + b, pc_.qcount + b + 1, pc_.scount + b, pc_.work + 3 * b + 1, pc_.totals);
             toc();
-            if (sd_->view.n_lights > 0) {
+            if (sd_->view.n_lights > 0 || ((opts_.extensions & PATHS_EXT_ENV_NEE) && sd_->view.sky_type == 2)) {
                 tic(3);
                 launch_shadow(b);
                 toc();

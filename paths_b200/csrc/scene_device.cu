@@ -179,7 +179,8 @@ SceneDevice *upload_scene(int device, const HostScene &hs, const RefTree *ref, c
             vn[3 * i + 2] = hs.vertex_normals[i].z;
         }
         ok = ok && put(sd, objs, &v.objects, err) && put(sd, lights, &v.lights, err) && put(sd, vn, &v.vertex_normals, err) &&
-             put(sd, hs.vertex_colours, &v.vertex_colours, err) && put(sd, hs.faces, &v.faces, err) && put(sd, hs.sky_texels, &v.sky_texels, err);
+             put(sd, hs.vertex_colours, &v.vertex_colours, err) && put(sd, hs.faces, &v.faces, err) && put(sd, hs.sky_texels, &v.sky_texels, err) &&
+             put(sd, hs.env_marginal, &v.env_marginal, err) && put(sd, hs.env_conditional, &v.env_conditional, err);
         v.sky_type = hs.sky_type;
         for (int k = 0; k < 3; k++) {
             v.sky_c0[k] = hs.sky_c0[k];
