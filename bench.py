@@ -247,39 +247,60 @@ def run_ours(args, rank, world, local_rank):
     ms_t, dt_, _ = timed_region(rt, args.steps, args.warmup, False)
     rt.shutdown()
 
+    # ---- end to end through the C ABI with host buffers, on all N GPUs: camera in (new epoch) on every rank, each rank renders
+    # its sample range, NCCL reduce of the float4 buffers to rank 0, RGB24 frame out to pinned host memory on rank 0, every step
+    import math
+
+    def rotation(yaw, pitch, roll):  # Matrix3::rotation (src/matrix.rs:30-35)
+        cp, sp, cy, sy, cr, sr = math.cos(pitch), math.sin(pitch), math.cos(yaw), math.sin(yaw), math.cos(roll), math.sin(roll)
+        rx = np.array([[1, 0, 0], [0, cp, -sp], [0, sp, cp]])
+        ry = np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]])
+        rz = np.array([[cr, -sr, 0], [sr, cr, 0], [0, 0, 1]])
+        return rx @ ry @ rz
+
+    re_ = make_renderer(False)
+    cam = scene.camera
+    rot = rotation(cam.yaw, cam.pitch, cam.roll)
+    loc = np.array(list(cam.location))
+    out = torch.empty((H, W, 3), dtype=torch.uint8, pin_memory=True).numpy() if rank == 0 else None
+    ext = torch.cuda.ExternalStream(re_.cuda_stream(), device=local_rank)
+    ptr, n, eb = re_.device_sums()
+    sums = torch.as_tensor(_DevView(ptr, n, eb), device=torch.device("cuda", local_rank))
+    frame = torch.empty_like(sums) if world > 1 else None
+
+    def e2e_step():
+        re_.set_camera(loc, rot)                      # host -> device: camera (new epoch, estimator cleared)
+        if world == 1:
+            re_.render_samples(S)                     # blocking render of S spp
+        else:
+            with torch.cuda.stream(ext):
+                re_.render_samples(S * world, wait=False)
+                frame.copy_(sums)
+                dist.reduce(frame, dst=0, op=dist.ReduceOp.SUM)
+                if rank == 0:
+                    sums.copy_(frame)                 # the combined estimator is what gets tonemapped
+            re_.sync()
+        if rank == 0:
+            pb.check(pb.lib().paths_renderer_image_rgb24(re_._h, out.ctypes.data))  # device -> host: tonemapped frame
+
+    e2e_steps = max(3, min(args.steps, 20))
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    barrier()
+    e2e_dt = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_dt], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_dt = float(t.item())
+    e2e_value = e2e_steps * S * world * W * H / e2e_dt
+    re_.shutdown()
+
     line = None
     if rank == 0:
-        # ---- end to end through the C ABI with host buffers: camera in (new epoch), RGB24 frame + stats out, every step
-        re_ = make_renderer(False) if world == 1 else pb.Renderer(scene.camera, scene, device=local_rank, precision=args.precision, seed=args.seed)
-        cam = scene.camera
-        import math
-
-        def rotation(yaw, pitch, roll):  # Matrix3::rotation (src/matrix.rs:30-35)
-            cp, sp, cy, sy, cr, sr = math.cos(pitch), math.sin(pitch), math.cos(yaw), math.sin(yaw), math.cos(roll), math.sin(roll)
-            rx = np.array([[1, 0, 0], [0, cp, -sp], [0, sp, cp]])
-            ry = np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]])
-            rz = np.array([[cr, -sr, 0], [sr, cr, 0], [0, 0, 1]])
-            return rx @ ry @ rz
-
-        rot = rotation(cam.yaw, cam.pitch, cam.roll)
-        loc = np.array(list(cam.location))
-        out = torch.empty((H, W, 3), dtype=torch.uint8, pin_memory=True).numpy()
-        e2e_steps = max(3, min(args.steps, 20))
-        for _ in range(2):
-            re_.set_camera(loc, rot)
-            re_.render_samples(S)
-            pb.check(pb.lib().paths_renderer_image_rgb24(re_._h, out.ctypes.data))
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        for _ in range(e2e_steps):
-            re_.set_camera(loc, rot)       # host -> device: camera (new epoch, estimator cleared)
-            re_.render_samples(S)          # blocking render of S spp
-            pb.check(pb.lib().paths_renderer_image_rgb24(re_._h, out.ctypes.data))  # device -> host: tonemapped frame
-        torch.cuda.synchronize()
-        e2e_dt = time.perf_counter() - t0
-        e2e_value = e2e_steps * S * W * H / e2e_dt
-        re_.shutdown()
-
         # ---- CPU baseline + algorithmic bytes (the only use of oracle/ in this arm)
         cpu, ctr, Q, per_sample = cpu_reference_leg(yaml, W, H, args.cpu_budget)
         peaks = {}
@@ -289,6 +310,14 @@ def run_ours(args, rank, world, local_rank):
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         ext_ms = dt_["ms_extend"]
+        # measured DRAM bytes per extend launch (dram__bytes_read.sum + dram__bytes_write.sum, one ncu capture of this workload)
+        traffic, traffic_src = None, None
+        try:
+            tj = json.loads((ROOT / "profiles" / "traffic.json").read_text()).get(f"{args.scene}:{S}")
+            if tj and world == 1:
+                traffic, traffic_src = tj["extend_bytes_per_launch"], tj["source"]
+        except (OSError, ValueError, KeyError):
+            pass
         n_ext_launch = max(dt_["n_extend_launches"], 1)
         ach = (Q * dt_["extend_rays"]) / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else 0.0
         line = {
@@ -303,10 +332,11 @@ def run_ours(args, rank, world, local_rank):
             "mrays_per_sec": (tot_ext + tot_shadow) / (ms * 1e-3) / 1e6,
             "rays_per_sample": (tot_ext + tot_shadow) / max(tot_samples, 1),
             "clocks": clocks,
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 12 * 8 + 208, "d2h_bytes_per_step": W * H * 3,
-                    "what": "set_camera (new epoch) + render + RGB24 frame to pinned host memory through the C ABI, 1 GPU"},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": (12 * 8 + 208) * world, "d2h_bytes_per_step": W * H * 3,
+                    "what": f"set_camera (new epoch) + render + RGB24 frame to pinned host memory through the C ABI on {world} GPU(s)"
+                            + (", NCCL reduce of the float4 buffers to rank 0 inside the timed region" if world > 1 else "")},
             "gpu_launches": int(tot_launch),
-            "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+            "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic, "traffic_source": traffic_src,
                          "kernel": "k_extend<float>", "launches": int(n_ext_launch), "avg_launch_ms": ext_ms / n_ext_launch,
                          "algorithmic_bytes_per_ray": Q, "algorithmic_bytes_per_sample": per_sample,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst)" if peaks else "fallback 6650",

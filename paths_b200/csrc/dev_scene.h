@@ -103,6 +103,18 @@ struct PassControl {
 struct ShardInfo {
     uint32_t n_local;         // pixels owned by this rank
     const uint32_t *pixels;   // local -> global pixel index, or NULL for identity
+    uint32_t n_local_magic;   // floor(2^32 / n_local): slot / n_local without an integer division (see shard_split)
+#if defined(__CUDACC__)
+    // slot -> (local pixel, sample within the pass); the estimate __umulhi(slot, magic) is at most one too small
+    __device__ __forceinline__ void split(uint32_t slot, uint32_t &lp, uint32_t &k) const {
+        k = __umulhi(slot, n_local_magic);
+        lp = slot - k * n_local;
+        if (lp >= n_local) {
+            lp -= n_local;
+            k += 1;
+        }
+    }
+#endif
 };
 
 } // namespace paths

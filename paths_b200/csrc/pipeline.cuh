@@ -31,6 +31,8 @@ template <> struct IsF64<double> {
 
 template <typename R> __device__ __forceinline__ typename Vec4T<R>::type ld4(const typename Vec4T<R>::type *p) { return *p; }
 
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 __device__ __forceinline__ uint32_t warp_fetch(uint32_t *cursor) {
     uint32_t base = 0;
     if ((threadIdx.x & 31u) == 0) base = atomicAdd(cursor, 32u);
@@ -54,7 +56,8 @@ __global__ void __launch_bounds__(256) k_raygen(DevCamera cam, uint32_t k0, uint
                                                 PathState<typename Vec4T<R>::type> ps, PassControl pc) {
     uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += stride) {
-        uint32_t lp = i % shard.n_local, k = i / shard.n_local;
+        uint32_t lp, k;
+        shard.split(i, lp, k);
         uint32_t pixel = shard.pixels ? shard.pixels[lp] : lp;
         V3<R> o, d;
         R w;
@@ -270,8 +273,25 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? 2 : PATHS_LB_SHADE)) k
                                                unsigned long long *totals) {
     const uint32_t count = *count_ptr;
     const uint32_t lane = threadIdx.x & 31u;
+    // cursor == nullptr: batches of 32 entries are dealt to the warps of the grid round-robin (shading cost per entry is
+    // uniform enough) -- no fetch atomic on the critical path; the next batch's records are prefetched into L2 meanwhile
+    const uint32_t warp_stride = gridDim.x * (blockDim.x >> 5) * 32u;
+    uint32_t static_base = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 32u;
     for (;;) {
-        uint32_t base = warp_fetch(cursor);
+        uint32_t base;
+        if (cursor) base = warp_fetch(cursor);
+        else {
+            base = static_base;
+            static_base += warp_stride;
+            uint32_t in = base + warp_stride + lane;
+            if (in < count && base < count) {
+                uint32_t sn = queue ? __ldg(queue + in) : in;
+                prefetch_l2(ps.ray_o + sn);
+                prefetch_l2(ps.ray_d + sn);
+                prefetch_l2(ps.hit + sn);
+                prefetch_l2(ps.thr + sn);
+            }
+        }
         if (base >= count) break;
         uint32_t i = base + lane;
         ShadeOut<R> out;
@@ -279,7 +299,8 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? 2 : PATHS_LB_SHADE)) k
         uint32_t slot = 0;
         if (i < count) {
             slot = queue ? queue[i] : i;
-            uint32_t lp = slot % shard.n_local, k = slot / shard.n_local;
+            uint32_t lp, k;
+            shard.split(slot, lp, k);
             uint32_t pixel = shard.pixels ? shard.pixels[lp] : lp;
             shade_path<R>(sc, ps, slot, pixel, s_base + k, k0, k1, max_bounces, ext, totals, out);
         }
@@ -652,6 +673,146 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_shadow4(DevScene sc, P
                     col.x += c.x; col.y += c.y; col.z += c.z;
                     if (col.x < 0.0f || col.y < 0.0f || col.z < 0.0f) atomicAdd(totals + 2, 1ull);
                     ps.col[slot] = col;
+                    has = false;
+                }
+            }
+        }
+    }
+}
+
+// Four-wide, speculative: a lane that reaches a leaf parks it (`pend`) and keeps descending from its stack; the inner phase of
+// a round ends when fewer than MIN_INNER lanes still have an inner node to visit (one ballot per step), so that the leaf phase
+// runs with most lanes of the warp (ncu on k_extend4: triangle tests ran with 3.6 of 32 lanes, box tests with 13.8).
+template <int ROUNDS, int MIN_REFILL, int KI, int MIN_INNER>
+__global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend4s(DevScene sc, PathState<float4> ps, const uint32_t *queue, const uint32_t *count_ptr,
+                                                                   uint32_t *cursor) {
+    extern __shared__ int32_t smem_stack[];
+    int32_t *sstack = smem_stack + threadIdx.x;
+    const uint32_t stride = blockDim.x;
+    const uint32_t count = *count_ptr;
+    const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    const float4 *__restrict__ nodes4 = sc.fast4_nodes;
+    const float4 *__restrict__ leaves = sc.fast_leaves;
+    TravF4 tv;
+    tv.node = PATHS_TRAV_DONE;
+    bool has = false, exhausted = false;
+    uint32_t slot = 0;
+    int32_t pend = 0;
+    for (;;) {
+        unsigned idle = __ballot_sync(PATHS_FULL_MASK, !has);
+        int n = __popc(idle);
+        if (!exhausted && n >= MIN_REFILL) {
+            int leader = __ffs(idle) - 1;
+            uint32_t base = 0;
+            if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)n);
+            base = __shfl_sync(PATHS_FULL_MASK, base, leader);
+            if (!has) {
+                uint32_t i = base + __popc(idle & lt);
+                if (i < count) {
+                    slot = queue ? queue[i] : i;
+                    float4 o = ps.ray_o[slot], d = ps.ray_d[slot];
+                    tv.init(o.x, o.y, o.z, d.x, d.y, d.z, __int_as_float(0x7f800000), sc.fast4_root);
+                    pend = 0;
+                    has = true;
+                }
+            }
+            exhausted = base + (uint32_t)n >= count;
+        }
+        if (!__any_sync(PATHS_FULL_MASK, has)) break;
+#pragma unroll 1
+        for (int r = 0; r < ROUNDS; r++) {
+            const int n_has = __popc(__ballot_sync(PATHS_FULL_MASK, has));
+#pragma unroll 1
+            for (int k = 0; k < KI; k++) {
+                bool inner = has && tv.node >= 0;
+                // leave the inner phase when nobody is at an inner node, or when few are and other lanes wait with a leaf
+                int n_inner = __popc(__ballot_sync(PATHS_FULL_MASK, inner));
+                if (n_inner == 0 || (n_inner < MIN_INNER && n_inner < n_has)) break;
+                if (inner) tv.inner4(nodes4, sstack, stride);
+                if (has && pend == 0 && tv.node < 0 && tv.node != PATHS_TRAV_DONE) {
+                    pend = tv.node;
+                    tv.node = tv.pop4(sstack, stride);
+                }
+            }
+            if (has) {
+                if (pend == 0 && tv.node < 0 && tv.node != PATHS_TRAV_DONE) { // reached while the inner phase was cut short
+                    pend = tv.node;
+                    tv.node = tv.pop4(sstack, stride);
+                }
+                if (pend != 0) {
+                    tv.leaf_test<false>(leaves, pend, 0xFFFFFFFFu);
+                    pend = 0;
+                }
+                if (tv.node == PATHS_TRAV_DONE) {
+                    ps.hit[slot] = make_float4(__uint_as_float(tv.prim), tv.t, tv.bx, tv.by);
+                    has = false;
+                }
+            }
+        }
+    }
+}
+
+// Two-wide counterpart (local-memory stack), same round structure.
+template <int ROUNDS, int MIN_REFILL, int KI, int MIN_INNER>
+__global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend2s(DevScene sc, PathState<float4> ps, const uint32_t *queue, const uint32_t *count_ptr,
+                                                                   uint32_t *cursor) {
+    const uint32_t count = *count_ptr;
+    const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    const float4 *__restrict__ nodes = sc.fast_nodes;
+    const float4 *__restrict__ leaves = sc.fast_leaves;
+    int32_t stack[PATHS_FAST_STACK];
+    TravF tv;
+    tv.node = PATHS_TRAV_DONE;
+    bool has = false, exhausted = false;
+    uint32_t slot = 0;
+    int32_t pend = 0;
+    for (;;) {
+        unsigned idle = __ballot_sync(PATHS_FULL_MASK, !has);
+        int n = __popc(idle);
+        if (!exhausted && n >= MIN_REFILL) {
+            int leader = __ffs(idle) - 1;
+            uint32_t base = 0;
+            if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)n);
+            base = __shfl_sync(PATHS_FULL_MASK, base, leader);
+            if (!has) {
+                uint32_t i = base + __popc(idle & lt);
+                if (i < count) {
+                    slot = queue ? queue[i] : i;
+                    float4 o = ps.ray_o[slot], d = ps.ray_d[slot];
+                    tv.init(o.x, o.y, o.z, d.x, d.y, d.z, __int_as_float(0x7f800000), sc.fast_root);
+                    pend = 0;
+                    has = true;
+                }
+            }
+            exhausted = base + (uint32_t)n >= count;
+        }
+        if (!__any_sync(PATHS_FULL_MASK, has)) break;
+#pragma unroll 1
+        for (int r = 0; r < ROUNDS; r++) {
+            const int n_has = __popc(__ballot_sync(PATHS_FULL_MASK, has));
+#pragma unroll 1
+            for (int k = 0; k < KI; k++) {
+                bool inner = has && tv.node >= 0;
+                // leave the inner phase when nobody is at an inner node, or when few are and other lanes wait with a leaf
+                int n_inner = __popc(__ballot_sync(PATHS_FULL_MASK, inner));
+                if (n_inner == 0 || (n_inner < MIN_INNER && n_inner < n_has)) break;
+                if (inner) tv.inner(nodes, stack);
+                if (has && pend == 0 && tv.node < 0 && tv.node != PATHS_TRAV_DONE) {
+                    pend = tv.node;
+                    tv.node = tv.pop(stack);
+                }
+            }
+            if (has) {
+                if (pend == 0 && tv.node < 0 && tv.node != PATHS_TRAV_DONE) {
+                    pend = tv.node;
+                    tv.node = tv.pop(stack);
+                }
+                if (pend != 0) {
+                    tv.leaf_test<false>(leaves, pend, 0xFFFFFFFFu);
+                    pend = 0;
+                }
+                if (tv.node == PATHS_TRAV_DONE) {
+                    ps.hit[slot] = make_float4(__uint_as_float(tv.prim), tv.t, tv.bx, tv.by);
                     has = false;
                 }
             }

@@ -16,7 +16,7 @@ template <typename R> class RendererImpl : public RendererBase {
     uint32_t W_, H_, npix_, n_local_ = 0, spp_pass_ = 1, n_ctl_ = 0;
     size_t n_slots_max_ = 0;
     uint32_t samples_done_ = 0; // global samples per pixel issued so far (all ranks together)
-    int sm_count_ = 148, grid_trace_ = 0, grid_shade_ = 0, grid_stream_ = 0, variant_ = 3, grid4_ = 0;
+    int sm_count_ = 148, grid_trace_ = 0, grid_shade_ = 0, grid_stream_ = 0, variant_ = 3, grid4_ = 0, shade_variant_ = 1;
     size_t smem4_ = 0;
     // device buffers
     R4 *sums_ = nullptr;
@@ -167,8 +167,9 @@ template <typename R> class RendererImpl : public RendererBase {
         PATHS_CU(cudaMemset(pc_.totals, 0, 4 * sizeof(unsigned long long)));
         // traversal kernel: two-wide nodes + local stack for small (L1-resident) scenes, four-wide nodes + shared-memory stack
         // above 64k primitives (measured: teapot 7.5 vs 7.8 ms, dragon 25.4 vs 24.4 ms per 16 spp; profiles/r01_*)
-        variant_ = sd_->view.n_prims > 65536u ? 12 : 3;
+        variant_ = sd_->view.n_prims > 65536u ? 16 : 3;
         if (const char *v = getenv("PATHS_EXTEND_VARIANT")) variant_ = atoi(v); // development switch between traversal kernels
+        if (const char *v = getenv("PATHS_SHADE_VARIANT")) shade_variant_ = atoi(v);
         // ---- persistent grids: every SM full
         int bps = 0;
         if constexpr (IsF64<R>::value) PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_extend<R>, 128, 0));
@@ -181,12 +182,16 @@ template <typename R> class RendererImpl : public RendererBase {
             // four-wide kernels: stack of 3 * depth + 1 levels per thread in shared memory
             smem4_ = (size_t)(3 * sd_->view.fast4_depth + 1) * 128 * sizeof(int32_t);
             if (smem4_ > 200 * 1024) {
-                if (variant_ >= 10) variant_ = 3; // pathological tree: the two-wide kernels keep their stack in local memory
+                if (variant_ >= 10 && variant_ < 20) variant_ = 3; // pathological tree: the two-wide kernels keep their stack in local memory
             } else {
                 PATHS_CU(cudaFuncSetAttribute(k_extend4<4, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
                 PATHS_CU(cudaFuncSetAttribute(k_extend4<4, 16, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
                 PATHS_CU(cudaFuncSetAttribute(k_extend4<2, 16, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
                 PATHS_CU(cudaFuncSetAttribute(k_shadow4<4, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
+                PATHS_CU(cudaFuncSetAttribute(k_extend4s<2, 16, 8, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
+                PATHS_CU(cudaFuncSetAttribute(k_extend4s<2, 16, 16, 12>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
+                PATHS_CU(cudaFuncSetAttribute(k_extend4s<4, 16, 8, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
+                PATHS_CU(cudaFuncSetAttribute(k_extend4s<1, 8, 16, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
                 PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_extend4<4, 16, 2>, 128, smem4_));
                 grid4_ = sm_count_ * std::max(bps, 1);
             }
@@ -211,6 +216,14 @@ template <typename R> class RendererImpl : public RendererBase {
             case 10: k_extend4<4, 16, 2><<<grid4_, 128, smem4_, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
             case 11: k_extend4<4, 16, 1><<<grid4_, 128, smem4_, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
             case 12: k_extend4<2, 16, 3><<<grid4_, 128, smem4_, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 13: k_extend4s<2, 16, 8, 8><<<grid4_, 128, smem4_, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 14: k_extend4s<2, 16, 16, 12><<<grid4_, 128, smem4_, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 15: k_extend4s<4, 16, 8, 16><<<grid4_, 128, smem4_, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 16: k_extend4s<1, 8, 16, 8><<<grid4_, 128, smem4_, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 20: k_extend2s<2, 16, 8, 8><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 21: k_extend2s<2, 16, 16, 12><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 22: k_extend2s<4, 16, 8, 16><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 23: k_extend2s<1, 8, 16, 8><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
             default: break;
             }
         }
@@ -218,7 +231,7 @@ template <typename R> class RendererImpl : public RendererBase {
     }
     void launch_shadow(uint32_t b) {
         if constexpr (!IsF64<R>::value) {
-            if (variant_ >= 10) {
+            if (variant_ >= 10 && variant_ < 20) {
                 k_shadow4<4, 16, 2><<<grid4_, 128, smem4_, stream_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
                 return;
             }
@@ -237,6 +250,7 @@ template <typename R> class RendererImpl : public RendererBase {
         ShardInfo shard;
         shard.n_local = n_local_;
         shard.pixels = pixels_;
+        shard.n_local_magic = n_local_ > 1 ? (uint32_t)((1ull << 32) / n_local_) : 0xFFFFFFFFu;
         const uint32_t nb = opts_.max_bounces + 1; // segments per path (trace.rs:13-16)
         PATHS_CU(cudaMemsetAsync(ctl_block_, 0, n_ctl_ * sizeof(uint32_t), stream_));
         tic(0);
@@ -251,7 +265,7 @@ template <typename R> class RendererImpl : public RendererBase {
             tic(2);
             k_shade<R><<<grid_shade_, 128, 0, stream_>>>(sd_->view, ps_, shard, s_base, k0, k1, opts_.max_bounces, opts_.extensions, q,
                                                         pc_.queue[(b + 1) & 1],
-                                                        pc_.qcount + b, pc_.qcount + b + 1, pc_.scount + b, pc_.work + 3 * b + 1, pc_.totals);
+                                                        pc_.qcount + b, pc_.qcount + b + 1, pc_.scount + b, shade_variant_ == 1 ? nullptr : pc_.work + 3 * b + 1, pc_.totals);
             toc();
             if (sd_->view.n_lights > 0 || ((opts_.extensions & PATHS_EXT_ENV_NEE) && sd_->view.sky_type == 2)) {
                 tic(3);

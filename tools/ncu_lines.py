@@ -31,27 +31,33 @@ iS, iI, iT, iSrc = h.index("# Samples"), h.index("Instructions Executed"), h.ind
 dis = subprocess.run(["nvdisasm", "-g", "-c", cubin], capture_output=True, text=True).stdout
 # find the function section for the kernel
 lines = dis.splitlines()
-start = None
-mangled = None
-for i, ln in enumerate(lines):
-    m = re.match(r"\s*\.text\.(\S+):", ln)
-    if m and ksub.split("<")[0].split("(")[0].split("::")[-1] in m.group(1):
-        start, mangled = i, m.group(1)
-        break
-if start is None:
-    sys.exit("kernel not found in cubin")
-seq, curline = [], ("?", 0)
-for ln in lines[start + 1:]:
-    if re.match(r"\s*\.text\.", ln) or ln.strip().startswith(".section"):
-        break
-    m = re.search(r'//## File "([^"]+)", line (\d+)', ln)
-    if m:
-        curline = (m.group(1).split("/")[-1], int(m.group(2)))
-        continue
-    m = re.match(r"\s*/\*([0-9a-f]{4,})\*/\s+(.*?);", ln)
-    if m:
-        seq.append((curline, m.group(2)))
 rows = b["rows"]
+key = ksub.split("<")[0].split("(")[0].split("::")[-1]
+starts = [(i, re.match(r"\s*\.text\.(\S+):", ln).group(1)) for i, ln in enumerate(lines) if re.match(r"\s*\.text\.(\S+):", ln)]
+starts = [(i, m) for i, m in starts if key in m]
+if not starts:
+    sys.exit("kernel not found in cubin")
+
+
+def disassemble(start):
+    seq, curline = [], ("?", 0)
+    for ln in lines[start + 1:]:
+        if re.match(r"\s*\.text\.", ln) or ln.strip().startswith(".section"):
+            break
+        m = re.search(r'//## File "([^"]+)", line (\d+)', ln)
+        if m:
+            curline = (m.group(1).split("/")[-1], int(m.group(2)))
+            continue
+        m = re.match(r"\s*/\*([0-9a-f]{4,})\*/\s+(.*?);", ln)
+        if m:
+            seq.append((curline, m.group(2)))
+    return seq
+
+
+# several template instantiations share the name: take the one whose instruction count matches the profiled kernel
+cands = [(abs(len(disassemble(i)) - len(rows)), i, m) for i, m in starts]
+_, start, mangled = min(cands)
+seq = disassemble(start)
 if len(seq) != len(rows):
     print(f"warning: {len(seq)} disassembled instructions vs {len(rows)} profiled", file=sys.stderr)
 agg = defaultdict(lambda: [0, 0, 0])
