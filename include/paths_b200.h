@@ -122,7 +122,7 @@ typedef struct paths_renderer paths_renderer;
 
 enum { PATHS_PRECISION_AUTO = 0, PATHS_PRECISION_F32 = 32, PATHS_PRECISION_F64 = 64 };
 enum { PATHS_SHARD_SAMPLES = 0, PATHS_SHARD_TILES = 1 };
-enum { PATHS_BVH_FAST = 0, PATHS_BVH_REFERENCE = 1 };
+enum { PATHS_BVH_FAST = 0, PATHS_BVH_REFERENCE = 1, PATHS_BVH_DEVICE = 2 };
 /* Estimator extensions that have NO reference behaviour; all off by default so that output stays in parity.
  *   ENV_NEE        next-event estimation toward an Hdri sky through a CDF table (the reference only looks the map up on a miss,
  *                  src/scene.rs:95-111); a sky miss then counts only after a specular bounce, like light hits do (trace.rs:31-41)
@@ -167,6 +167,11 @@ typedef struct {
     int32_t auto_precision;     /* what PATHS_PRECISION_AUTO resolves to for this scene */
     double bounds_min[3], bounds_max[3]; /* of prims with radius/extent < 1e5 */
     double build_ms_ref, build_ms_fast;
+    /* production tree built on the GPU (PATHS_BVH_DEVICE); zeros until a device build has run */
+    double build_ms_device;     /* CUDA-event time of the last device build */
+    uint32_t bvh_builder;       /* builder of the production tree staged last: 0 host SAH, 1 device morton (LBVH) */
+    uint32_t device_nodes2, device_nodes4, device_depth2, device_depth4;
+    uint32_t giant_prims;       /* primitives chained above the morton root (the scenes' 1e6-radius plane spheres) */
 } paths_scene_info;
 
 /* ------------------------------------------------------------------ scene (replaces SceneDescription::scene + Scene::new,
@@ -185,6 +190,13 @@ void paths_scene_destroy(paths_scene *s);
 /* construct_bvh_aac (src/bvh.rs:160-206) on the host, ahead of first use: which = PATHS_BVH_REFERENCE builds the reference-order
  * AAC tree the f64 kernels traverse, PATHS_BVH_FAST the production SAH tree.  Trees are otherwise built lazily. */
 paths_status paths_scene_build_bvh(paths_scene *s, int32_t which);
+/* which = PATHS_BVH_DEVICE selects the GPU builder for the production tree instead (morton codes, radix sort, Karras
+ * hierarchy, bottom-up boxes with an SAH leaf decision -- milliseconds for ~1M triangles): it runs on each device at staging time;
+ * scenes with fewer than 64 ordinary primitives keep the host builder.  PATHS_BVH_FAST switches back.  Either call drops the
+ * production trees already staged, so renderers created afterwards use the new tree; existing renderers keep theirs.
+ * paths_scene_check_bvh walks the production tree staged on `device` (staging it first if needed) on the host and counts
+ * violations: a visible primitive missing from or repeated in the leaves, a primitive or child box sticking out of its parent's box. */
+paths_status paths_scene_check_bvh(paths_scene *s, int32_t device, uint32_t *violations);
 paths_status paths_scene_get_info(const paths_scene *s, paths_scene_info *info);
 /* per-prim identity as the reference reports it: (is_light, entity id, face index) (bvh.rs T6, geom.rs:48-57) */
 /* flattened geometry of one item after Mesh::primitives / TrianglePrimitive::transform (src/geom.rs:111-117,251-261):

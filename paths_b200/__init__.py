@@ -158,10 +158,17 @@ class Scene:
         check(lib().paths_scene_get_info(self._h, C.byref(si)))
         return si.as_dict()
 
-    def build_bvh(self, reference=False):
-        """construct_bvh_aac (src/bvh.rs:160-206) when reference=True, else the production tree; returns `info`."""
-        check(lib().paths_scene_build_bvh(self._h, 1 if reference else 0))
+    def build_bvh(self, reference=False, device=False):
+        """construct_bvh_aac (src/bvh.rs:160-206) when reference=True, else the production tree: the host SAH builder, or with
+        device=True the GPU morton builder (runs at staging time on each device); returns `info`."""
+        check(lib().paths_scene_build_bvh(self._h, 2 if device else (1 if reference else 0)))
         return self.info
+
+    def check_bvh(self, device=0):
+        """Walks the production tree staged on `device` on the host; returns the number of structural violations."""
+        bad = C.c_uint32(0)
+        check(lib().paths_scene_check_bvh(self._h, device, C.byref(bad)))
+        return bad.value
 
     def prim_entity(self, prim):
         il, en, fa = C.c_int32(), C.c_uint32(), C.c_uint32()

@@ -90,7 +90,9 @@ class SceneInfo(C.Structure):
     _fields_ = [("n_prims", C.c_uint32), ("n_triangles", C.c_uint32), ("n_spheres", C.c_uint32), ("n_objects", C.c_uint32),
                 ("n_lights", C.c_uint32), ("ref_nodes", C.c_uint32), ("ref_depth", C.c_uint32), ("fast_nodes", C.c_uint32),
                 ("fast_depth", C.c_uint32), ("hidden_prims", C.c_uint32), ("auto_precision", C.c_int32), ("bounds_min", C.c_double * 3),
-                ("bounds_max", C.c_double * 3), ("build_ms_ref", C.c_double), ("build_ms_fast", C.c_double)]
+                ("bounds_max", C.c_double * 3), ("build_ms_ref", C.c_double), ("build_ms_fast", C.c_double), ("build_ms_device", C.c_double),
+                ("bvh_builder", C.c_uint32), ("device_nodes2", C.c_uint32), ("device_nodes4", C.c_uint32), ("device_depth2", C.c_uint32),
+                ("device_depth4", C.c_uint32), ("giant_prims", C.c_uint32)]
 
     def as_dict(self):
         out = {}
@@ -111,6 +113,7 @@ SIGNATURES = {
     "paths_scene_destroy": (None, [VP]),
     "paths_scene_build_bvh": (C.c_int, [VP, C.c_int32]),
     "paths_scene_get_info": (C.c_int, [VP, C.POINTER(SceneInfo)]),
+    "paths_scene_check_bvh": (C.c_int, [VP, C.c_int32, C.POINTER(C.c_uint32)]),
     "paths_scene_prim_geometry": (C.c_int, [VP, C.c_uint32, VP, C.POINTER(C.c_int32)]),
     "paths_scene_prim_entity": (C.c_int, [VP, C.c_uint32, C.POINTER(C.c_int32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
     "paths_trace_closest": (C.c_int, [VP, C.c_int32, VP, VP, C.c_size_t, VP, VP, VP, C.c_int32]),

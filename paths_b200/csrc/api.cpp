@@ -3,7 +3,9 @@
 #include <chrono>
 #include <cstdio>
 #include <cstring>
+#include <algorithm>
 #include <exception>
+#include <limits>
 #include <mutex>
 #include <new>
 #include <string>
@@ -32,15 +34,22 @@ struct paths_scene {
     RefTree ref;
     FastTree fast;
     bool has_ref = false, has_fast = false;
+    bool device_build = false; // PATHS_BVH_DEVICE: production tree built by bvh_device.cu at staging time
     double ms_ref = 0.0, ms_fast = 0.0;
+    DeviceTreeInfo dev_info;   // of the last device build
+    uint32_t last_builder = 0;
     struct Staged {
         SceneDevice *sd;
         bool ref, fast;
+        bool device_tree;
+        DeviceTreeInfo info;
     };
+    std::vector<SceneDevice *> retired; // staged copies replaced by a builder switch: renderers may still use them
     std::vector<Staged> staged;
     std::mutex mu;
     ~paths_scene() {
         for (Staged &s : staged) delete s.sd;
+        for (SceneDevice *sd : retired) delete sd;
     }
 };
 
@@ -78,17 +87,45 @@ paths_status ensure_staged(paths_scene *s, int device, bool need_ref, bool need_
         s->ms_ref = now_ms() - t0;
         s->has_ref = true;
     }
+    if (need_fast && s->device_build) {
+        // the GPU builder works on the prim tables in HBM: stage without a production tree, then build in place
+        SceneDevice *sd = upload_scene(device, s->hs, s->has_ref ? &s->ref : nullptr, nullptr, err);
+        if (!sd) return fail(PATHS_ERR_CUDA, err);
+        DeviceTreeInfo info;
+        if (build_device_tree(sd, s->hs, info, err)) {
+            s->dev_info = info;
+            s->last_builder = 1;
+            s->staged.push_back(paths_scene::Staged{sd, s->has_ref, true, true, info});
+            *out = sd;
+            return PATHS_OK;
+        }
+        delete sd;
+        if (err != "small") return fail(PATHS_ERR_CUDA, err);
+    }
     if (need_fast && !s->has_fast) {
         double t0 = now_ms();
         if (!build_fast_tree(s->hs, s->fast, err)) return fail(PATHS_ERR_INTERNAL, err);
         s->ms_fast = now_ms() - t0;
         s->has_fast = true;
     }
-    SceneDevice *sd = upload_scene(device, s->hs, s->has_ref ? &s->ref : nullptr, s->has_fast ? &s->fast : nullptr, err);
+    // with the device builder selected, a host tree left over from before is only staged when the device build declined ("small")
+    const FastTree *ft = (s->has_fast && (!s->device_build || need_fast)) ? &s->fast : nullptr;
+    SceneDevice *sd = upload_scene(device, s->hs, s->has_ref ? &s->ref : nullptr, ft, err);
     if (!sd) return fail(PATHS_ERR_CUDA, err);
-    s->staged.push_back(paths_scene::Staged{sd, s->has_ref, s->has_fast});
+    if (ft) s->last_builder = 0;
+    s->staged.push_back(paths_scene::Staged{sd, s->has_ref, ft != nullptr, false, DeviceTreeInfo()});
     *out = sd;
     return PATHS_OK;
+}
+
+// a builder switch: staged copies that carry a production tree are set aside (renderers created earlier keep using them)
+void retire_fast_staged(paths_scene *s) {
+    std::vector<paths_scene::Staged> keep;
+    for (paths_scene::Staged &st : s->staged) {
+        if (st.fast) s->retired.push_back(st.sd);
+        else keep.push_back(st);
+    }
+    s->staged.swap(keep);
 }
 
 int resolve_precision(const paths_scene *s, int32_t precision) {
@@ -184,10 +221,202 @@ paths_status paths_scene_build_bvh(paths_scene *s, int32_t which) {
             s->ms_fast = now_ms() - t0;
             s->has_fast = true;
         }
+        if (s->device_build) retire_fast_staged(s);
+        s->device_build = false;
+    } else if (which == PATHS_BVH_DEVICE) {
+        if (!s->device_build) retire_fast_staged(s);
+        s->device_build = true;
     } else return fail(PATHS_ERR_INVALID_ARG, "unknown tree kind");
     return PATHS_OK;
     PATHS_GUARD_END
 }
+
+} // extern "C" (reopened below)
+
+namespace {
+struct TreeCheck {
+    const HostScene &hs;
+    const std::vector<float> &leaves;
+    std::vector<uint32_t> seen;
+    uint32_t bad = 0;
+    size_t visited = 0;
+    explicit TreeCheck(const HostScene &h, const std::vector<float> &l) : hs(h), leaves(l), seen(h.prims.size(), 0) {}
+    static bool inside(const float *ilo, const float *ihi, const float *olo, const float *ohi) {
+        for (int a = 0; a < 3; a++)
+            if (!(ilo[a] >= olo[a] && ihi[a] <= ohi[a])) return false;
+        return true;
+    }
+    // every primitive of leaf `code` lies inside (lo, hi)
+    void leaf(int32_t code, const float *lo, const float *hi) {
+        uint32_t c = (uint32_t)~code, first = c >> 3, cnt = (c & 7u) + 1u;
+        for (uint32_t k = first; k < first + cnt; k++) {
+            if (12 * (size_t)k + 12 > leaves.size()) {
+                bad++;
+                continue;
+            }
+            uint32_t tag;
+            std::memcpy(&tag, &leaves[12 * (size_t)k + 11], 4);
+            uint32_t prim = tag & 0x7FFFFFFFu;
+            if (prim >= hs.prims.size()) {
+                bad++;
+                continue;
+            }
+            seen[prim]++;
+            const HostPrim &p = hs.prims[prim];
+            float plo[3], phi[3];
+            if (p.type == 1) {
+                const D3 *v[3] = {&p.a, &p.b, &p.c};
+                for (int a = 0; a < 3; a++) {
+                    plo[a] = std::numeric_limits<float>::infinity();
+                    phi[a] = -plo[a];
+                }
+                for (int j = 0; j < 3; j++) {
+                    float f[3] = {(float)v[j]->x, (float)v[j]->y, (float)v[j]->z};
+                    for (int a = 0; a < 3; a++) {
+                        plo[a] = std::min(plo[a], f[a]);
+                        phi[a] = std::max(phi[a], f[a]);
+                    }
+                }
+            } else { // the box of a sphere was rounded outward from f64: compare in f64
+                double c3[3] = {p.a.x, p.a.y, p.a.z};
+                bool ok = true;
+                for (int a = 0; a < 3; a++) ok = ok && (double)lo[a] <= c3[a] - p.b.x && (double)hi[a] >= c3[a] + p.b.x;
+                if (!ok) bad++;
+                continue;
+            }
+            if (!inside(plo, phi, lo, hi)) bad++;
+        }
+    }
+    void finish() {
+        for (size_t i = 0; i < hs.prims.size(); i++) {
+            const HostPrim &p = hs.prims[i];
+            bool hidden = p.type == 1 && (p.box.lo.x == p.box.hi.x || p.box.lo.y == p.box.hi.y || p.box.lo.z == p.box.hi.z);
+            if (seen[i] != (hidden ? 0u : 1u)) bad++;
+        }
+    }
+};
+
+// two-wide: 16 floats per node {c0 lo.x hi.x lo.y hi.y | c1 ... | c0 lo.z hi.z c1 lo.z hi.z | codes}
+uint32_t check_tree2(const HostScene &hs, const std::vector<float> &nodes, const std::vector<float> &leaves, int32_t root) {
+    TreeCheck tc(hs, leaves);
+    if (root == (int32_t)0x80000000) {
+        tc.finish();
+        return tc.bad;
+    }
+    struct Item {
+        int32_t node;
+        float lo[3], hi[3];
+        bool has_box;
+    };
+    std::vector<Item> stack;
+    Item r;
+    r.node = root;
+    r.has_box = false;
+    stack.push_back(r);
+    while (!stack.empty()) {
+        Item it = stack.back();
+        stack.pop_back();
+        if (it.node < 0 || 16 * (size_t)it.node + 16 > nodes.size() || ++tc.visited > nodes.size() / 16 + 1) {
+            tc.bad++;
+            continue;
+        }
+        const float *n = &nodes[16 * (size_t)it.node];
+        int32_t codes[2];
+        std::memcpy(codes, n + 12, 8);
+        for (int c = 0; c < 2; c++) {
+            Item ch;
+            ch.lo[0] = n[4 * c + 0]; ch.hi[0] = n[4 * c + 1]; ch.lo[1] = n[4 * c + 2]; ch.hi[1] = n[4 * c + 3];
+            ch.lo[2] = n[8 + 2 * c]; ch.hi[2] = n[9 + 2 * c];
+            if (!(ch.lo[0] <= ch.hi[0])) continue; // empty slot (single-leaf wrapper)
+            if (it.has_box && !TreeCheck::inside(ch.lo, ch.hi, it.lo, it.hi)) tc.bad++;
+            if (c == 1 && codes[1] == codes[0] && codes[0] < 0) continue; // wrapper repeats its only leaf
+            if (codes[c] < 0) tc.leaf(codes[c], ch.lo, ch.hi);
+            else {
+                ch.node = codes[c];
+                ch.has_box = true;
+                stack.push_back(ch);
+            }
+        }
+    }
+    tc.finish();
+    return tc.bad;
+}
+
+// four-wide: 32 floats per node {lox[4] hix[4] loy[4] hiy[4] loz[4] hiz[4] codes[4] pad[4]}
+uint32_t check_tree4(const HostScene &hs, const std::vector<float> &nodes, const std::vector<float> &leaves, int32_t root) {
+    TreeCheck tc(hs, leaves);
+    if (root == (int32_t)0x80000000) {
+        tc.finish();
+        return tc.bad;
+    }
+    struct Item {
+        int32_t node;
+        float lo[3], hi[3];
+        bool has_box;
+    };
+    std::vector<Item> stack;
+    Item r;
+    r.node = root;
+    r.has_box = false;
+    stack.push_back(r);
+    while (!stack.empty()) {
+        Item it = stack.back();
+        stack.pop_back();
+        if (it.node < 0 || 32 * (size_t)it.node + 32 > nodes.size() || ++tc.visited > nodes.size() / 32 + 1) {
+            tc.bad++;
+            continue;
+        }
+        const float *n = &nodes[32 * (size_t)it.node];
+        int32_t codes[4];
+        std::memcpy(codes, n + 24, 16);
+        for (int c = 0; c < 4; c++) {
+            if (codes[c] == 0x7FFFFFFF) continue;
+            Item ch;
+            ch.lo[0] = n[c]; ch.hi[0] = n[4 + c]; ch.lo[1] = n[8 + c]; ch.hi[1] = n[12 + c]; ch.lo[2] = n[16 + c]; ch.hi[2] = n[20 + c];
+            if (it.has_box && !TreeCheck::inside(ch.lo, ch.hi, it.lo, it.hi)) tc.bad++;
+            if (codes[c] < 0) tc.leaf(codes[c], ch.lo, ch.hi);
+            else {
+                ch.node = codes[c];
+                ch.has_box = true;
+                stack.push_back(ch);
+            }
+        }
+    }
+    tc.finish();
+    return tc.bad;
+}
+} // namespace
+
+paths_status paths_scene_check_bvh(paths_scene *s, int32_t device, uint32_t *violations) {
+    PATHS_GUARD_BEGIN
+    if (!s || !violations) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    paths_status st = check_device(device);
+    if (st != PATHS_OK) return st;
+    const SceneDevice *sd = nullptr;
+    st = ensure_staged(s, device, false, true, &sd);
+    if (st != PATHS_OK) return st;
+    DeviceTreeInfo info;
+    {
+        std::lock_guard<std::mutex> lock(s->mu);
+        for (paths_scene::Staged &e : s->staged)
+            if (e.sd == sd) {
+                if (e.device_tree) info = e.info;
+                else {
+                    info.nodes2 = (uint32_t)s->fast.nodes.size();
+                    info.nodes4 = (uint32_t)s->fast.nodes4.size();
+                    info.leaves = (uint32_t)s->fast.leaf_prims.size();
+                }
+            }
+    }
+    std::vector<float> n2, n4, lv;
+    std::string err;
+    if (!download_fast_tree(sd, info, n2, n4, lv, err)) return fail(PATHS_ERR_CUDA, err);
+    *violations = check_tree2(s->hs, n2, lv, sd->view.fast_root) + check_tree4(s->hs, n4, lv, sd->view.fast4_root);
+    return PATHS_OK;
+    PATHS_GUARD_END
+}
+
+extern "C" {
 
 paths_status paths_scene_get_info(const paths_scene *s, paths_scene_info *info) {
     if (!s || !info) return fail(PATHS_ERR_INVALID_ARG, "null argument");
@@ -211,6 +440,13 @@ paths_status paths_scene_get_info(const paths_scene *s, paths_scene_info *info) 
     info->bounds_max[0] = s->hs.bounds_hi.x; info->bounds_max[1] = s->hs.bounds_hi.y; info->bounds_max[2] = s->hs.bounds_hi.z;
     info->build_ms_ref = s->ms_ref;
     info->build_ms_fast = s->ms_fast;
+    info->build_ms_device = s->dev_info.ms;
+    info->bvh_builder = s->last_builder;
+    info->device_nodes2 = s->dev_info.nodes2;
+    info->device_nodes4 = s->dev_info.nodes4;
+    info->device_depth2 = s->dev_info.depth2;
+    info->device_depth4 = s->dev_info.depth4;
+    info->giant_prims = s->dev_info.giants;
     return PATHS_OK;
 }
 

@@ -19,6 +19,18 @@ struct SceneDevice {
 // Uploads the scene; ref / fast may be null (the matching kernels then must not be used).
 SceneDevice *upload_scene(int device, const HostScene &hs, const RefTree *ref, const FastTree *fast, std::string &err);
 
+// ---- production tree built on the device (bvh_device.cu)
+struct DeviceTreeInfo {
+    float ms = 0.0f;                 // CUDA-event time of the whole build, scratch allocation included
+    uint32_t nodes2 = 0, nodes4 = 0; // node slots allocated (two-wide: Karras index space, not all referenced)
+    uint32_t depth2 = 0, depth4 = 0;
+    uint32_t giants = 0, leaves = 0, hidden = 0;
+};
+// false + err == "small": too few ordinary primitives for a morton build, use the host builder
+bool build_device_tree(SceneDevice *sd, const HostScene &hs, DeviceTreeInfo &info, std::string &err);
+bool download_fast_tree(const SceneDevice *sd, const DeviceTreeInfo &info, std::vector<float> &nodes2, std::vector<float> &nodes4,
+                        std::vector<float> &leaves, std::string &err);
+
 struct RendererBase {
     virtual ~RendererBase() {}
     virtual paths_status render(uint32_t spp, bool wait) = 0;

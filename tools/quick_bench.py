@@ -18,6 +18,10 @@ import make_assets  # noqa: E402
 
 make_assets.ensure("dragon", "hdri", "doom", "table")
 sc = pb.Scene.load(scene, width=W, height=H)
+import os  # noqa: E402
+
+if os.environ.get("PATHS_BVH_DEVICE"):
+    sc.build_bvh(device=True)
 for timed in (False, True):
     r = pb.Renderer(sc.camera, sc, precision=prec, seed=1, time_kernels=timed, samples_per_pass=spass)
     r.render_samples(min(spp, 4))  # warm-up
