@@ -186,6 +186,10 @@ paths_status paths_scene_create(const paths_scene_desc *desc, paths_scene **out)
  * then against the YAML's parent directory).  width/height = 0 keep the file's values. */
 paths_status paths_scene_load_yaml(const char *yaml_path, const char *asset_root, uint32_t width, uint32_t height,
                                    paths_scene **out, paths_camera *camera);
+/* generate_stress_scene (src/stress.rs:7-66; the scene src/main.rs:47-50 renders when no file is given, with 500 spheres): random
+ * spheres with random Gloss / Lambertian / Mirror materials under a flat grey sky, no lights, and the reference's fixed camera.  The
+ * reference draws from an unseedable thread_rng; here a SplitMix64 stream started at `seed` is consumed in the reference's order. */
+paths_status paths_scene_create_stress(uint32_t num_spheres, uint64_t seed, paths_scene **out, paths_camera *camera);
 void paths_scene_destroy(paths_scene *s);
 /* construct_bvh_aac (src/bvh.rs:160-206) on the host, ahead of first use: which = PATHS_BVH_REFERENCE builds the reference-order
  * AAC tree the f64 kernels traverse, PATHS_BVH_FAST the production SAH tree.  Trees are otherwise built lazily. */
@@ -240,6 +244,23 @@ paths_status paths_renderer_get_stats(paths_renderer *r, paths_stats *st);
 paths_status paths_renderer_set_camera(paths_renderer *r, const double location[3], const double rot[9]);
 /* reset() (renderer.rs:122-128) */
 paths_status paths_renderer_reset(paths_renderer *r);
+
+/* ---- the interactive front half of Renderer (src/renderer.rs:143-192), single GPU.
+ * render_preview = request_preview (renderer.rs:152-164): one sample for every 6th pixel in x and y.  The image calls show a pixel
+ * that has no samples yet through that grid, like Estimator::render (src/pixels.rs:53-79).
+ * render_columns = the next n_requests of next_request (renderer.rs:166-192): whole pixel columns from the centre of the image
+ * outwards, 1 sample per pixel during the first sweep of an epoch ((1,1) pattern), 25 per sweep afterwards ((5,5) pattern).  A sweep
+ * of all columns advances every pixel exactly like paths_renderer_render(1) resp. (25) -- the estimator is bit-identical.
+ * paths_renderer_render refuses to run in the middle of a sweep.  get_progress: samples per pixel completed by whole-frame calls and
+ * finished sweeps, and the number of columns already rendered in the sweep in progress. */
+paths_status paths_renderer_render_preview(paths_renderer *r);
+paths_status paths_renderer_render_columns(paths_renderer *r, uint32_t n_requests);
+paths_status paths_renderer_get_progress(paths_renderer *r, uint32_t *samples_per_pixel, uint32_t *sweep_position);
+/* Checkpoint / resume (the reference keeps its Estimator in memory only and loses it on exit): the per-pixel sums and counts plus
+ * the position in the sample schedule.  A renderer that loads a checkpoint (same image size and seed) and renders k more samples
+ * holds the same estimator as one that rendered without interruption. */
+paths_status paths_renderer_save_checkpoint(paths_renderer *r, const char *path);
+paths_status paths_renderer_load_checkpoint(paths_renderer *r, const char *path);
 /* shutdown() (renderer.rs:130-141) */
 void paths_renderer_destroy(paths_renderer *r);
 

@@ -402,16 +402,27 @@ def load_scene_yaml(yaml_path, asset_root=None, width=None, height=None):
 
 
 def stress_scene(num_spheres=500, seed=0):
-    """src/stress.rs:7-66 with a seeded generator (the reference's is unseedable)."""
-    rng = np.random.default_rng(seed)
+    """src/stress.rs:7-66 with a seeded generator (the reference's thread_rng is unseedable): SplitMix64 consumed in the reference's
+    draw order -- centre x, y, z, radius, material choice, colour r, g, b, then the Gloss reflectance."""
+    mask = (1 << 64) - 1
+    state = [seed & mask]
+
+    def unit():
+        state[0] = (state[0] + 0x9E3779B97F4A7C15) & mask
+        z = state[0]
+        z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & mask
+        z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & mask
+        z ^= z >> 31
+        return (z >> 11) * (1.0 / 9007199254740992.0)
+
     objects = []
     for _ in range(num_spheres):
-        center = [rng.random() * 100.0 - 50.0, rng.random() * 100.0 - 50.0, rng.random() * 100.0]
-        radius = rng.random() * 5.0
-        choice = int(rng.integers(0, 3))
-        colour = [rng.random(), rng.random(), rng.random()]
+        center = [unit() * 100.0 - 50.0, unit() * 100.0 - 50.0, unit() * 100.0]
+        radius = unit() * 5.0
+        choice = int(unit() * 3.0)
+        colour = [unit(), unit(), unit()]
         if choice == 0:
-            mat = {"type": "Gloss", "albedo": {"type": "Rgb", "rgb": colour}, "reflectance": 1.0 + rng.random() * 2.0, "metalness": 0.0}
+            mat = {"type": "Gloss", "albedo": {"type": "Rgb", "rgb": colour}, "reflectance": 1.0 + unit() * 2.0, "metalness": 0.0}
         elif choice == 1:
             mat = {"type": "Lambertian", "albedo": {"type": "Rgb", "rgb": colour}}
         else:

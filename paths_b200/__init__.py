@@ -141,6 +141,14 @@ class Scene:
                                           C.byref(h), C.byref(cam)))
         return cls(_handle=h, camera=cam)
 
+    @classmethod
+    def stress(cls, num_spheres=500, seed=0):
+        """generate_stress_scene (src/stress.rs:7-66), seeded; what the reference renders when started without a scene file."""
+        h = C.c_void_p()
+        cam = Camera()
+        check(lib().paths_scene_create_stress(int(num_spheres), int(seed), C.byref(h), C.byref(cam)))
+        return cls(_handle=h, camera=cam)
+
     def close(self):
         if self._h:
             lib().paths_scene_destroy(self._h)
@@ -278,6 +286,27 @@ class Renderer:
 
     def reset(self):
         check(lib().paths_renderer_reset(self._h))
+
+    # -- the interactive front half (renderer.rs:143-192)
+    def request_preview(self):
+        """renderer.rs:152-164: one sample for every 6th pixel; `render()` fills unsampled pixels from that grid (pixels.rs:53-79)."""
+        check(lib().paths_renderer_render_preview(self._h))
+
+    def render_columns(self, n_requests):
+        """The next `n_requests` column requests of next_request (renderer.rs:166-192), centre outwards."""
+        check(lib().paths_renderer_render_columns(self._h, int(n_requests)))
+
+    def progress(self):
+        """(samples per pixel completed, columns done in the sweep in progress)."""
+        a, b = C.c_uint32(), C.c_uint32()
+        check(lib().paths_renderer_get_progress(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def save_checkpoint(self, path):
+        check(lib().paths_renderer_save_checkpoint(self._h, str(path).encode()))
+
+    def load_checkpoint(self, path):
+        check(lib().paths_renderer_load_checkpoint(self._h, str(path).encode()))
 
     def shutdown(self):
         if self._h:

@@ -110,6 +110,7 @@ SIGNATURES = {
     "paths_device_count": (C.c_int, [C.POINTER(C.c_int32)]),
     "paths_scene_create": (C.c_int, [C.POINTER(SceneDesc), C.POINTER(VP)]),
     "paths_scene_load_yaml": (C.c_int, [C.c_char_p, C.c_char_p, C.c_uint32, C.c_uint32, C.POINTER(VP), C.POINTER(Camera)]),
+    "paths_scene_create_stress": (C.c_int, [C.c_uint32, C.c_uint64, C.POINTER(VP), C.POINTER(Camera)]),
     "paths_scene_destroy": (None, [VP]),
     "paths_scene_build_bvh": (C.c_int, [VP, C.c_int32]),
     "paths_scene_get_info": (C.c_int, [VP, C.POINTER(SceneInfo)]),
@@ -131,6 +132,11 @@ SIGNATURES = {
     "paths_renderer_get_stats": (C.c_int, [VP, C.POINTER(Stats)]),
     "paths_renderer_set_camera": (C.c_int, [VP, VP, VP]),
     "paths_renderer_reset": (C.c_int, [VP]),
+    "paths_renderer_render_preview": (C.c_int, [VP]),
+    "paths_renderer_render_columns": (C.c_int, [VP, C.c_uint32]),
+    "paths_renderer_get_progress": (C.c_int, [VP, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
+    "paths_renderer_save_checkpoint": (C.c_int, [VP, C.c_char_p]),
+    "paths_renderer_load_checkpoint": (C.c_int, [VP, C.c_char_p]),
     "paths_renderer_destroy": (None, [VP]),
     "paths_camera_rays": (C.c_int, [C.POINTER(Camera), C.c_int32, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
                                     VP, VP, VP, C.c_int32]),

@@ -57,6 +57,7 @@ struct paths_renderer {
     RendererBase *impl = nullptr;
     paths_scene *scene = nullptr;
     uint32_t w = 0, h = 0;
+    uint64_t seed = 0;
     ~paths_renderer() { delete impl; }
 };
 
@@ -197,6 +198,64 @@ paths_status paths_scene_load_yaml(const char *yaml_path, const char *asset_root
     *camera = ls.camera;
     *out = s;
     return PATHS_OK;
+    PATHS_GUARD_END
+}
+
+// generate_stress_scene (src/stress.rs:7-66) with a seedable generator: the reference draws from thread_rng, which cannot be seeded.
+// Draw order follows the reference: centre x, y, z, radius (random_sphere), then material choice, colour r, g, b and, for Gloss,
+// the reflectance (random_material).  SplitMix64; f64 = top 53 bits * 2^-53 (what rand 0.6.5's gen::<f64>() does with its own bits).
+paths_status paths_scene_create_stress(uint32_t num_spheres, uint64_t seed, paths_scene **out, paths_camera *camera) {
+    PATHS_GUARD_BEGIN
+    if (!out || !camera) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    *out = nullptr;
+    uint64_t state = seed;
+    auto next = [&state]() {
+        uint64_t z = (state += 0x9E3779B97F4A7C15ull);
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        return z ^ (z >> 31);
+    };
+    auto unit = [&next]() { return (double)(next() >> 11) * (1.0 / 9007199254740992.0); };
+    std::vector<paths_object_desc> objs(num_spheres);
+    for (paths_object_desc &o : objs) {
+        std::memset(&o, 0, sizeof(o));
+        o.shape = 0;
+        o.smooth_normals = 1;
+        o.scale = 1.0;
+        o.center[0] = unit() * 100.0 - 50.0;
+        o.center[1] = unit() * 100.0 - 50.0;
+        o.center[2] = unit() * 100.0;
+        o.radius = unit() * 5.0;
+        int choice = (int)(unit() * 3.0); // gen_range(0, 3)
+        double colour[3] = {unit(), unit(), unit()};
+        paths_basic_material &m = o.material.m;
+        for (int k = 0; k < 3; k++) m.albedo[k] = colour[k];
+        if (choice == 0) {
+            m.type = PATHS_MAT_GLOSS;
+            m.reflectance = 1.0 + unit() * 2.0;
+            m.metalness = 0.0;
+        } else if (choice == 1) m.type = PATHS_MAT_LAMBERTIAN;
+        else {
+            m.type = PATHS_MAT_MIRROR;
+            for (int k = 0; k < 3; k++) m.albedo[k] = 0.0;
+        }
+    }
+    paths_scene_desc desc;
+    std::memset(&desc, 0, sizeof(desc));
+    desc.n_objects = num_spheres;
+    desc.objects = objs.data();
+    desc.sky.type = 0; // Flat 0.8 grey, no lights
+    for (int k = 0; k < 3; k++) desc.sky.c0[k] = 0.8;
+    paths_camera cam;
+    std::memset(&cam, 0, sizeof(cam));
+    cam.image_width = 720;
+    cam.image_height = 480;
+    cam.location[0] = 0.0; cam.location[1] = -5.0; cam.location[2] = -13.0;
+    cam.pitch = 0.0; cam.yaw = 0.0; cam.roll = -0.3;
+    cam.sensor_width = 0.036; cam.sensor_height = 0.024; cam.focal_length = 0.05; cam.focus_distance = 10.0; cam.aperture = 8.0;
+    paths_status st = paths_scene_create(&desc, out);
+    if (st == PATHS_OK) *camera = cam;
+    return st;
     PATHS_GUARD_END
 }
 
@@ -531,6 +590,7 @@ paths_status paths_renderer_create(paths_scene *s, const paths_camera *cam, cons
     r->scene = s;
     r->w = cam->image_width;
     r->h = cam->image_height;
+    r->seed = opts.seed;
     *out = r;
     return PATHS_OK;
     PATHS_GUARD_END
@@ -579,6 +639,77 @@ paths_status paths_renderer_set_camera(paths_renderer *r, const double location[
     PATHS_FORWARD(r->impl->set_camera(location, rot))
 }
 paths_status paths_renderer_reset(paths_renderer *r) { PATHS_FORWARD(r->impl->reset()) }
+paths_status paths_renderer_render_preview(paths_renderer *r) { PATHS_FORWARD(r->impl->render_preview()) }
+paths_status paths_renderer_render_columns(paths_renderer *r, uint32_t n_requests) { PATHS_FORWARD(r->impl->render_columns(n_requests)) }
+paths_status paths_renderer_get_progress(paths_renderer *r, uint32_t *samples_per_pixel, uint32_t *sweep_position) {
+    if (!samples_per_pixel || !sweep_position) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    PATHS_FORWARD(r->impl->get_progress(samples_per_pixel, sweep_position))
+}
+
+// ---- checkpoint / resume: the estimator (sum + count per pixel) and the position in the sample schedule are the whole state
+namespace {
+struct CheckpointHeader {
+    char magic[8]; // "PATHSCK1"
+    uint32_t width, height;
+    uint32_t samples_done;
+    uint32_t reserved;
+    uint64_t seed;
+};
+} // namespace
+
+paths_status paths_renderer_save_checkpoint(paths_renderer *r, const char *path) {
+    PATHS_GUARD_BEGIN
+    if (!r || !path) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    uint32_t done = 0, sweep = 0;
+    paths_status st = r->impl->get_progress(&done, &sweep);
+    if (st != PATHS_OK) return fail(st, r->impl->err);
+    if (sweep != 0) return fail(PATHS_ERR_INVALID_ARG, "a column sweep is in progress: checkpoints are taken between sweeps");
+    std::vector<double> sums((size_t)r->w * r->h * 4);
+    st = r->impl->get_sums(sums.data());
+    if (st != PATHS_OK) return fail(st, r->impl->err);
+    CheckpointHeader h;
+    std::memset(&h, 0, sizeof(h));
+    std::memcpy(h.magic, "PATHSCK1", 8);
+    h.width = r->w;
+    h.height = r->h;
+    h.samples_done = done;
+    h.seed = r->seed;
+    FILE *f = std::fopen(path, "wb");
+    if (!f) return fail(PATHS_ERR_IO, std::string("cannot open ") + path);
+    bool ok = std::fwrite(&h, sizeof(h), 1, f) == 1 && std::fwrite(sums.data(), sizeof(double), sums.size(), f) == sums.size();
+    ok = (std::fclose(f) == 0) && ok;
+    return ok ? PATHS_OK : fail(PATHS_ERR_IO, std::string("short write to ") + path);
+    PATHS_GUARD_END
+}
+
+paths_status paths_renderer_load_checkpoint(paths_renderer *r, const char *path) {
+    PATHS_GUARD_BEGIN
+    if (!r || !path) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    FILE *f = std::fopen(path, "rb");
+    if (!f) return fail(PATHS_ERR_IO, std::string("cannot open ") + path);
+    CheckpointHeader h;
+    std::vector<double> sums;
+    bool ok = std::fread(&h, sizeof(h), 1, f) == 1 && std::memcmp(h.magic, "PATHSCK1", 8) == 0;
+    if (ok && (h.width != r->w || h.height != r->h)) {
+        std::fclose(f);
+        return fail(PATHS_ERR_INVALID_ARG, "checkpoint was taken at another image size");
+    }
+    if (ok && h.seed != r->seed) {
+        std::fclose(f);
+        return fail(PATHS_ERR_INVALID_ARG, "checkpoint was taken with another seed: resuming would repeat or skip samples");
+    }
+    if (ok) {
+        sums.resize((size_t)h.width * h.height * 4);
+        ok = std::fread(sums.data(), sizeof(double), sums.size(), f) == sums.size();
+    }
+    std::fclose(f);
+    if (!ok) return fail(PATHS_ERR_PARSE, std::string("not a checkpoint file: ") + path);
+    paths_status st = r->impl->reset(); // new epoch, then the saved estimator on top of zeros
+    if (st == PATHS_OK) st = r->impl->add_sums(sums.data());
+    if (st == PATHS_OK) st = r->impl->set_progress(h.samples_done);
+    return st == PATHS_OK ? st : fail(st, r->impl->err);
+    PATHS_GUARD_END
+}
 void paths_renderer_destroy(paths_renderer *r) { delete r; }
 
 paths_status paths_camera_rays(const paths_camera *cam, int32_t device, uint64_t seed, uint32_t sample, uint32_t x0, uint32_t y0, uint32_t w,

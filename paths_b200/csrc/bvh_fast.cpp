@@ -8,6 +8,7 @@
 // (src/bvh.rs:16) and is therefore invisible; such primitives are left out of this tree.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <thread>
@@ -59,8 +60,8 @@ struct SNode {
 };
 
 const int kBins = 16;
-const uint32_t kMaxLeaf = 4;
-const float kTraversalCost = 1.0f, kPrimCost = 1.2f;
+uint32_t kMaxLeaf = 4;
+float kTraversalCost = 1.0f, kPrimCost = 1.2f;
 
 struct Sah {
     std::vector<Ref> refs;
@@ -268,6 +269,8 @@ uint32_t emit4(const std::vector<SNode> &sn, int node, FastTree &out, int32_t &c
 } // namespace
 
 bool build_fast_tree(const HostScene &s, FastTree &out, std::string &err) {
+    if (const char *v = getenv("PATHS_SAH_MAXLEAF")) kMaxLeaf = (uint32_t)std::min(8, std::max(1, atoi(v))); // development switches
+    if (const char *v = getenv("PATHS_SAH_PRIMCOST")) kPrimCost = (float)atof(v);
     std::vector<Ref> refs;
     refs.reserve(s.prims.size());
     // The slab test evaluates lo * (1/d) - o * (1/d): its error is about one ulp of the ORIGIN's coordinate, wherever the box is.

@@ -1,6 +1,9 @@
 // cli_main.cpp -- headless stand-in for the reference's SDL2 front end (src/main.rs:39-186): scene YAML in, image out.
-//   paths_cli scene.yml [--spp N] [--width W --height H] [--out img.ppm] [--pfm img.pfm] [--seed S] [--device D]
-//             [--precision 32|64] [--rank R --world N --shard samples|tiles]
+//   paths_cli [scene.yml] [--spp N] [--width W --height H] [--out img.ppm] [--pfm img.pfm] [--seed S] [--device D]
+//             [--precision 32|64] [--rank R --world N --shard samples|tiles] [--bvh host|device] [--stress N]
+//             [--resume file.ck] [--checkpoint file.ck] [--sweeps K]
+// Without a scene file the seeded 500-sphere stress scene is rendered, like the reference does (src/main.rs:47-50).
+// --sweeps K renders progressively instead of --spp: a preview pass, then K centre-out column sweeps (src/renderer.rs:152-192).
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -16,16 +19,19 @@ static int die(const char *what) {
 }
 
 int main(int argc, char **argv) {
-    if (argc < 2) {
-        std::fprintf(stderr, "usage: %s scene.yml [--spp N] [--width W] [--height H] [--out img.ppm] [--pfm img.pfm] [--seed S] [--device D] "
-                             "[--precision 32|64] [--rank R] [--world N] [--shard samples|tiles]\n", argv[0]);
+    if (argc >= 2 && (std::strcmp(argv[1], "-h") == 0 || std::strcmp(argv[1], "--help") == 0)) {
+        std::fprintf(stderr, "usage: %s [scene.yml] [--spp N] [--width W] [--height H] [--out img.ppm] [--pfm img.pfm] [--seed S] [--device D] "
+                             "[--precision 32|64] [--rank R] [--world N] [--shard samples|tiles] [--bvh host|device] [--stress N] "
+                             "[--resume file.ck] [--checkpoint file.ck] [--sweeps K]\n", argv[0]);
         return 2;
     }
-    std::string scene_path = argv[1], out = "out.ppm", pfm;
-    uint32_t spp = 64, width = 0, height = 0;
+    int first_opt = (argc >= 2 && std::strncmp(argv[1], "--", 2) != 0) ? 2 : 1;
+    std::string scene_path = first_opt == 2 ? argv[1] : "", out = "out.ppm", pfm, resume, checkpoint;
+    uint32_t spp = 64, width = 0, height = 0, stress = 500, sweeps = 0;
+    bool device_bvh = false;
     paths_render_opts opts;
     paths_render_opts_default(&opts);
-    for (int i = 2; i + 1 < argc; i += 2) {
+    for (int i = first_opt; i + 1 < argc; i += 2) {
         std::string k = argv[i];
         const char *v = argv[i + 1];
         if (k == "--spp") spp = (uint32_t)atoi(v);
@@ -38,6 +44,11 @@ int main(int argc, char **argv) {
         else if (k == "--precision") opts.precision = atoi(v);
         else if (k == "--rank") opts.rank = (uint32_t)atoi(v);
         else if (k == "--world") opts.world = (uint32_t)atoi(v);
+        else if (k == "--bvh") device_bvh = std::strcmp(v, "device") == 0;
+        else if (k == "--stress") stress = (uint32_t)atoi(v);
+        else if (k == "--resume") resume = v;
+        else if (k == "--checkpoint") checkpoint = v;
+        else if (k == "--sweeps") sweeps = (uint32_t)atoi(v);
         else if (k == "--shard") opts.shard_mode = std::strcmp(v, "tiles") == 0 ? PATHS_SHARD_TILES : PATHS_SHARD_SAMPLES;
         else {
             std::fprintf(stderr, "unknown option %s\n", k.c_str());
@@ -46,11 +57,22 @@ int main(int argc, char **argv) {
     }
     paths_scene *scene = nullptr;
     paths_camera cam;
-    if (paths_scene_load_yaml(scene_path.c_str(), nullptr, width, height, &scene, &cam) != PATHS_OK) return die("load");
+    if (scene_path.empty()) {
+        std::printf("No scene file passed in, generating random stress scene...\n"); // src/main.rs:48
+        if (paths_scene_create_stress(stress, opts.seed, &scene, &cam) != PATHS_OK) return die("stress scene");
+        if (width) cam.image_width = width;
+        if (height) cam.image_height = height;
+    } else if (paths_scene_load_yaml(scene_path.c_str(), nullptr, width, height, &scene, &cam) != PATHS_OK) return die("load");
+    if (device_bvh && paths_scene_build_bvh(scene, PATHS_BVH_DEVICE) != PATHS_OK) return die("bvh");
     paths_renderer *r = nullptr;
     if (paths_renderer_create(scene, &cam, &opts, &r) != PATHS_OK) return die("renderer");
+    if (!resume.empty() && paths_renderer_load_checkpoint(r, resume.c_str()) != PATHS_OK) return die("resume");
     auto t0 = std::chrono::steady_clock::now();
-    if (paths_renderer_render(r, spp) != PATHS_OK) return die("render");
+    if (sweeps > 0) {
+        if (paths_renderer_render_preview(r) != PATHS_OK) return die("preview");
+        if (paths_renderer_render_columns(r, sweeps * cam.image_width) != PATHS_OK) return die("render");
+    } else if (paths_renderer_render(r, spp) != PATHS_OK) return die("render");
+    if (!checkpoint.empty() && paths_renderer_save_checkpoint(r, checkpoint.c_str()) != PATHS_OK) return die("checkpoint");
     double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     paths_stats st;
     paths_renderer_get_stats(r, &st);

@@ -22,17 +22,23 @@ namespace paths {
     } while (0)
 
 // ------------------------------------------------------------------ small output kernels
-// Estimator::render (pixels.rs:53-79): mean = sum / count; zero-count pixels are left black (the preview-grid fill is UI only)
-template <typename R> __global__ void k_image_f32(const typename Vec4T<R>::type *sums, uint32_t n, float *rgb) {
+#define PATHS_PREVIEW_GRID 6u /* renderer.rs:13 */
+// Estimator::render (pixels.rs:53-79): mean = sum / count; a pixel without samples shows the preview-grid pixel above-left of it
+// (x - x % 6, y - y % 6); MeanVec::get of a pixel that has no samples either is 0/0 = NaN, which Colour::to_bytes turns into 0.
+template <typename R> __device__ __forceinline__ typename Vec4T<R>::type estimator_pixel(const typename Vec4T<R>::type *sums, uint32_t i, uint32_t W) {
+    typename Vec4T<R>::type s = sums[i];
+    if (s.w > R(0)) return s;
+    uint32_t x = i % W, y = i / W;
+    return sums[(x - x % PATHS_PREVIEW_GRID) + (y - y % PATHS_PREVIEW_GRID) * W];
+}
+template <typename R> __global__ void k_image_f32(const typename Vec4T<R>::type *sums, uint32_t n, uint32_t W, float *rgb) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    typename Vec4T<R>::type s = sums[i];
-    R inv = s.w > R(0) ? R(1) / s.w : R(0);
-    bool has = s.w > R(0);
+    typename Vec4T<R>::type s = estimator_pixel<R>(sums, i, W);
+    bool has = s.w > R(0); // the float image reports pixels that nothing covers as 0 rather than NaN
     rgb[3 * i] = has ? (float)(s.x / s.w) : 0.0f;
     rgb[3 * i + 1] = has ? (float)(s.y / s.w) : 0.0f;
     rgb[3 * i + 2] = has ? (float)(s.z / s.w) : 0.0f;
-    (void)inv;
 }
 // Colour::component_to_byte (colour.rs:62-74); Rust `as u8` saturates and maps NaN to 0
 template <typename R> __device__ __forceinline__ uint8_t to_byte(R x) {
@@ -44,10 +50,10 @@ template <typename R> __device__ __forceinline__ uint8_t to_byte(R x) {
     if (v >= R(255.0)) return 255;
     return (uint8_t)v;
 }
-template <typename R> __global__ void k_image_rgb24(const typename Vec4T<R>::type *sums, uint32_t n, uint8_t *rgb) {
+template <typename R> __global__ void k_image_rgb24(const typename Vec4T<R>::type *sums, uint32_t n, uint32_t W, uint8_t *rgb) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    typename Vec4T<R>::type s = sums[i];
+    typename Vec4T<R>::type s = estimator_pixel<R>(sums, i, W);
     bool has = s.w > R(0);
     rgb[3 * i] = has ? to_byte<R>(s.x / s.w) : 0;
     rgb[3 * i + 1] = has ? to_byte<R>(s.y / s.w) : 0;

@@ -21,6 +21,10 @@ template <typename R> class RendererImpl : public RendererBase {
     // device buffers
     R4 *sums_ = nullptr;
     uint32_t *pixels_ = nullptr; // tile shard: local -> global pixel
+    // interactive front half (renderer.rs:143-192): column sweeps from the centre outwards, preview grid
+    uint32_t *sweep_pixels_ = nullptr; // scratch local -> global table for column / preview passes [npix_]
+    uint32_t sweep_pos_ = 0;           // Renderer::block_num: requests issued in the current sweep
+    uint32_t n_previews_ = 0;
     PathState<R4> ps_;
     PassControl pc_;
     uint32_t *ctl_block_ = nullptr;
@@ -243,14 +247,17 @@ template <typename R> class RendererImpl : public RendererBase {
         k_shadow<R><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
     }
 
-    paths_status run_pass(uint32_t s_base, uint32_t n_spp) {
-        const uint32_t n_slots = n_local_ * n_spp;
+    paths_status run_pass(uint32_t s_base, uint32_t n_spp) { return run_pass_on(pixels_, n_local_, s_base, n_spp); }
+
+    // one wavefront pass over `n_local` pixels (`pixels` = local -> global index, or null for the whole frame in order)
+    paths_status run_pass_on(const uint32_t *pixels, uint32_t n_local, uint32_t s_base, uint32_t n_spp) {
+        const uint32_t n_slots = n_local * n_spp;
         if (n_slots == 0) return PATHS_OK;
         const uint32_t k0 = (uint32_t)opts_.seed, k1 = (uint32_t)(opts_.seed >> 32);
         ShardInfo shard;
-        shard.n_local = n_local_;
-        shard.pixels = pixels_;
-        shard.n_local_magic = n_local_ > 1 ? (uint32_t)((1ull << 32) / n_local_) : 0xFFFFFFFFu;
+        shard.n_local = n_local;
+        shard.pixels = pixels;
+        shard.n_local_magic = n_local > 1 ? (uint32_t)((1ull << 32) / n_local) : 0xFFFFFFFFu;
         const uint32_t nb = opts_.max_bounces + 1; // segments per path (trace.rs:13-16)
         PATHS_CU(cudaMemsetAsync(ctl_block_, 0, n_ctl_ * sizeof(uint32_t), stream_));
         tic(0);
@@ -286,6 +293,10 @@ template <typename R> class RendererImpl : public RendererBase {
 
     paths_status render(uint32_t spp, bool wait) override {
         PATHS_CU(cudaSetDevice(sd_->device));
+        if (sweep_pos_ != 0) {
+            err = "a column sweep is in progress: finish it with render_columns() or reset() before render()";
+            return PATHS_ERR_INVALID_ARG;
+        }
         uint32_t world = std::max<uint32_t>(opts_.world, 1);
         uint32_t s0 = samples_done_, s1 = samples_done_ + spp;
         if (opts_.shard_mode == PATHS_SHARD_SAMPLES && world > 1) { // this rank's slice of the sample range
@@ -314,7 +325,7 @@ template <typename R> class RendererImpl : public RendererBase {
         PATHS_CU(cudaSetDevice(sd_->device));
         float *d = nullptr;
         PATHS_CU(cudaMalloc(&d, (size_t)npix_ * 12));
-        k_image_f32<R><<<(npix_ + 255) / 256, 256, 0, stream_>>>(sums_, npix_, d);
+        k_image_f32<R><<<(npix_ + 255) / 256, 256, 0, stream_>>>(sums_, npix_, W_, d);
         cudaError_t e = cudaMemcpyAsync(rgb, d, (size_t)npix_ * 12, cudaMemcpyDeviceToHost, stream_);
         if (e == cudaSuccess) e = cudaStreamSynchronize(stream_);
         cudaFree(d);
@@ -325,7 +336,7 @@ template <typename R> class RendererImpl : public RendererBase {
         PATHS_CU(cudaSetDevice(sd_->device));
         uint8_t *d = nullptr;
         PATHS_CU(cudaMalloc(&d, (size_t)npix_ * 3));
-        k_image_rgb24<R><<<(npix_ + 255) / 256, 256, 0, stream_>>>(sums_, npix_, d);
+        k_image_rgb24<R><<<(npix_ + 255) / 256, 256, 0, stream_>>>(sums_, npix_, W_, d);
         cudaError_t e = cudaMemcpyAsync(rgb, d, (size_t)npix_ * 3, cudaMemcpyDeviceToHost, stream_);
         if (e == cudaSuccess) e = cudaStreamSynchronize(stream_);
         cudaFree(d);
@@ -390,8 +401,88 @@ template <typename R> class RendererImpl : public RendererBase {
         PATHS_CU(cudaMemset(sums_, 0, (size_t)npix_ * sizeof(R4)));
         PATHS_CU(cudaMemset(pc_.totals, 0, 4 * sizeof(unsigned long long)));
         samples_done_ = 0;
+        sweep_pos_ = 0;
+        n_previews_ = 0;
         resolve_timers();
         std::memset(&stats_, 0, sizeof(stats_));
+        return PATHS_OK;
+    }
+
+    // ---- interactive front half -------------------------------------------------------------------------------------------
+    paths_status ensure_sweep_table() {
+        if (!sweep_pixels_ && alloc(&sweep_pixels_, npix_) != PATHS_OK) return PATHS_ERR_CUDA;
+        return PATHS_OK;
+    }
+    paths_status single_gpu_only(const char *what) {
+        if (std::max<uint32_t>(opts_.world, 1) > 1) {
+            err = std::string(what) + " is a single-GPU call (world must be 1)";
+            return PATHS_ERR_UNSUPPORTED;
+        }
+        return PATHS_OK;
+    }
+    // Renderer::request_preview (renderer.rs:152-164): one sample for every 6th pixel in x and y, accumulated like any other
+    // sample; Estimator::render then fills pixels without samples from that grid (pixels.rs:53-79, see k_image_*).
+    paths_status render_preview() override {
+        PATHS_CU(cudaSetDevice(sd_->device));
+        paths_status st = single_gpu_only("render_preview");
+        if (st != PATHS_OK) return st;
+        if ((st = ensure_sweep_table()) != PATHS_OK) return st;
+        std::vector<uint32_t> px;
+        for (uint32_t x = 0; x < W_; x += PATHS_PREVIEW_GRID) // column-major like the reference's request order
+            for (uint32_t y = 0; y < H_; y += PATHS_PREVIEW_GRID) px.push_back(x + y * W_);
+        PATHS_CU(cudaMemcpyAsync(sweep_pixels_, px.data(), px.size() * 4, cudaMemcpyHostToDevice, stream_));
+        PATHS_CU(cudaStreamSynchronize(stream_)); // px is a stack-owned staging buffer
+        // preview samples use their own index range so that they never repeat a sample of the regular schedule
+        st = run_pass_on(sweep_pixels_, (uint32_t)px.size(), 0x40000000u + n_previews_, 1);
+        n_previews_++;
+        return st == PATHS_OK ? sync() : st;
+    }
+    // Renderer::next_request + fill/drain (renderer.rs:79-110,166-192): the next `n_requests` pixel columns, from the centre of the
+    // image outwards; one sample per pixel ((1,1) pattern) during the first sweep of an epoch, 25 ((5,5) pattern) afterwards.
+    // For odd widths the reference's formula asks for the centre column twice and never for column 0; here the repeat goes to
+    // column 0, so that every column is rendered once per sweep.
+    paths_status render_columns(uint32_t n_requests) override {
+        PATHS_CU(cudaSetDevice(sd_->device));
+        paths_status st = single_gpu_only("render_columns");
+        if (st != PATHS_OK) return st;
+        if ((st = ensure_sweep_table()) != PATHS_OK) return st;
+        std::vector<uint32_t> px;
+        while (n_requests > 0) {
+            const uint32_t n_spp = samples_done_ == 0 ? 1u : 25u; // quick_render (renderer.rs:172-176)
+            const uint32_t max_cols = std::max<uint32_t>(1, (uint32_t)std::min<size_t>(n_slots_max_ / ((size_t)H_ * n_spp), 0xFFFFFFFFu));
+            if ((size_t)H_ * n_spp > n_slots_max_) {
+                err = "samples_per_pass too small for one 25-sample column request";
+                return PATHS_ERR_INVALID_ARG;
+            }
+            uint32_t take = std::min({n_requests, W_ - sweep_pos_, max_cols});
+            px.clear();
+            for (uint32_t k = 0; k < take; k++) {
+                uint32_t n = sweep_pos_ + k;
+                uint32_t x = (n % 2 == 0) ? (W_ + n) / 2 : (W_ - n) / 2; // renderer.rs:170
+                if ((W_ & 1u) && n == 1) x = 0;                          // odd width: the repeated centre column (see above)
+                for (uint32_t y = 0; y < H_; y++) px.push_back(x + y * W_);
+            }
+            PATHS_CU(cudaMemcpyAsync(sweep_pixels_, px.data(), px.size() * 4, cudaMemcpyHostToDevice, stream_));
+            PATHS_CU(cudaStreamSynchronize(stream_));
+            if ((st = run_pass_on(sweep_pixels_, (uint32_t)px.size(), samples_done_, n_spp)) != PATHS_OK) return st;
+            PATHS_CU(cudaStreamSynchronize(stream_)); // the table is rewritten by the next chunk
+            sweep_pos_ += take;
+            n_requests -= take;
+            if (sweep_pos_ >= W_) { // renderer.rs:180-183
+                sweep_pos_ = 0;
+                samples_done_ += n_spp;
+            }
+        }
+        return sync();
+    }
+    paths_status get_progress(uint32_t *samples_done, uint32_t *sweep_pos) override {
+        *samples_done = samples_done_;
+        *sweep_pos = sweep_pos_;
+        return PATHS_OK;
+    }
+    paths_status set_progress(uint32_t samples_done) override { // checkpoint resume: continue the sample schedule where it stopped
+        samples_done_ = samples_done;
+        sweep_pos_ = 0;
         return PATHS_OK;
     }
 };

@@ -44,6 +44,10 @@ struct RendererBase {
     virtual paths_status get_stats(paths_stats *st) = 0;
     virtual paths_status set_camera(const double loc[3], const double rot[9]) = 0;
     virtual paths_status reset() = 0;
+    virtual paths_status render_preview() = 0;
+    virtual paths_status render_columns(uint32_t n_requests) = 0;
+    virtual paths_status get_progress(uint32_t *samples_done, uint32_t *sweep_pos) = 0;
+    virtual paths_status set_progress(uint32_t samples_done) = 0;
     std::string err;
 };
 
