@@ -120,7 +120,7 @@ typedef struct paths_renderer paths_renderer;
 
 /* ------------------------------------------------------------------ options */
 
-enum { PATHS_PRECISION_AUTO = 0, PATHS_PRECISION_F32 = 32, PATHS_PRECISION_F64 = 64 };
+enum { PATHS_PRECISION_AUTO = 0, PATHS_PRECISION_F32 = 32, PATHS_PRECISION_MIXED = 48, PATHS_PRECISION_F64 = 64 };
 enum { PATHS_SHARD_SAMPLES = 0, PATHS_SHARD_TILES = 1 };
 enum { PATHS_BVH_FAST = 0, PATHS_BVH_REFERENCE = 1, PATHS_BVH_DEVICE = 2 };
 /* Estimator extensions that have NO reference behaviour; all off by default so that output stays in parity.
@@ -135,7 +135,9 @@ enum { PATHS_EXT_ENV_NEE = 1, PATHS_EXT_MICROFACET = 2, PATHS_EXT_MICROFACET_COS
 
 typedef struct {
     int32_t device;        /* CUDA ordinal */
-    int32_t precision;     /* PATHS_PRECISION_*: F32 = production kernels, F64 = parity instantiation */
+    int32_t precision;     /* PATHS_PRECISION_*: F32 = production kernels; F64 = parity instantiation (the reference's tree and visiting
+                            * order); MIXED = f64 path state, shading and primitive tests over the production tree with f32 box tests --
+                            * what AUTO picks for scenes whose coordinates are too large for f32 rays (beyond +-128 units) */
     int32_t shard_mode;    /* PATHS_SHARD_* */
     uint32_t rank, world;  /* this renderer's shard; world = 0 or 1 means unsharded */
     uint64_t seed;         /* key of the counter-based RNG (the reference's thread_rng is unseedable) */

@@ -11,7 +11,7 @@ import ctypes as C
 import numpy as np
 
 from . import _capi
-from ._capi import (EXT_ENV_NEE, EXT_GGX, EXT_MICROFACET, EXT_MICROFACET_COSINE, EXT_NEE_ALL_LIGHTS, MISS, PRECISION_AUTO, PRECISION_F32, PRECISION_F64, SHARD_SAMPLES, SHARD_TILES, Camera, PathsError,  # noqa: F401
+from ._capi import (EXT_ENV_NEE, EXT_GGX, EXT_MICROFACET, EXT_MICROFACET_COSINE, EXT_NEE_ALL_LIGHTS, MISS, PRECISION_AUTO, PRECISION_F32, PRECISION_F64, PRECISION_MIXED, SHARD_SAMPLES, SHARD_TILES, Camera, PathsError,  # noqa: F401
                     RenderOpts, SceneInfo, Stats, build, check, lib)
 
 __all__ = ["Scene", "Renderer", "Image", "Camera", "PathsError", "build", "lib", "camera_rays", "device_count", "MISS"]

@@ -14,7 +14,7 @@ LIB_PATH = _PKG / "lib" / "libpaths_b200.so"
 
 OK, ERR_INVALID_ARG, ERR_IO, ERR_PARSE, ERR_CUDA, ERR_UNSUPPORTED, ERR_INTERNAL = range(7)
 MISS = 0xFFFFFFFF
-PRECISION_AUTO, PRECISION_F32, PRECISION_F64 = 0, 32, 64
+PRECISION_AUTO, PRECISION_F32, PRECISION_MIXED, PRECISION_F64 = 0, 32, 48, 64
 SHARD_SAMPLES, SHARD_TILES = 0, 1
 EXT_ENV_NEE, EXT_MICROFACET, EXT_MICROFACET_COSINE, EXT_GGX, EXT_NEE_ALL_LIGHTS = 1, 2, 4, 8, 16
 MAT_TYPES = {"Lambertian": 0, "Mirror": 1, "Gloss": 2, "CookTorrance": 3, "Fresnel": 4}

@@ -130,7 +130,7 @@ void retire_fast_staged(paths_scene *s) {
 }
 
 int resolve_precision(const paths_scene *s, int32_t precision) {
-    if (precision == PATHS_PRECISION_F32 || precision == PATHS_PRECISION_F64) return precision;
+    if (precision == PATHS_PRECISION_F32 || precision == PATHS_PRECISION_F64 || precision == PATHS_PRECISION_MIXED) return precision;
     return s->hs.auto_precision;
 }
 
@@ -546,10 +546,12 @@ paths_status paths_trace_closest(paths_scene *s, int32_t device, const double *o
     if (st != PATHS_OK) return st;
     int prec = resolve_precision(s, precision);
     const SceneDevice *sd = nullptr;
-    st = ensure_staged(s, device, prec == 64, prec == 32, &sd);
+    st = ensure_staged(s, device, prec == PATHS_PRECISION_F64, prec != PATHS_PRECISION_F64, &sd);
     if (st != PATHS_OK) return st;
     std::string err;
-    st = prec == 64 ? trace_closest_f64(sd, origins, dirs, n, prim_id, t, bary, err) : trace_closest_f32(sd, origins, dirs, n, prim_id, t, bary, err);
+    st = prec == PATHS_PRECISION_F64     ? trace_closest_f64(sd, origins, dirs, n, prim_id, t, bary, err)
+         : prec == PATHS_PRECISION_MIXED ? trace_closest_mixed(sd, origins, dirs, n, prim_id, t, bary, err)
+                                         : trace_closest_f32(sd, origins, dirs, n, prim_id, t, bary, err);
     return st == PATHS_OK ? st : fail(st, err);
     PATHS_GUARD_END
 }
@@ -580,10 +582,10 @@ paths_status paths_renderer_create(paths_scene *s, const paths_camera *cam, cons
     int prec = resolve_precision(s, opts.precision);
     opts.precision = prec;
     const SceneDevice *sd = nullptr;
-    st = ensure_staged(s, opts.device, prec == 64, prec == 32, &sd);
+    st = ensure_staged(s, opts.device, prec == PATHS_PRECISION_F64, prec != PATHS_PRECISION_F64, &sd);
     if (st != PATHS_OK) return st;
     std::string err;
-    RendererBase *impl = prec == 64 ? make_renderer_f64(sd, *cam, opts, err) : make_renderer_f32(sd, *cam, opts, err);
+    RendererBase *impl = prec == PATHS_PRECISION_F32 ? make_renderer_f32(sd, *cam, opts, err) : make_renderer_f64(sd, *cam, opts, err);
     if (!impl) return fail(PATHS_ERR_CUDA, err);
     paths_renderer *r = new paths_renderer();
     r->impl = impl;

@@ -290,6 +290,82 @@ template <bool ANY> __device__ __forceinline__ HitF trace_fast(const DevScene &s
     }
 }
 
+// ------------------------------------------------------------------ mixed traversal: production tree, f64 primitives
+// For scenes whose coordinates are too large for f32 rays (the integrator offsets new origins by an absolute 1e-4, trace.rs:57,89)
+// but which should not pay for the reference's own tree: f32 slab tests over the production SAH tree with the f64 ray rounded
+// to f32 (the boxes are padded by 4 ulps of the scene's extent, which covers that rounding), and the reference's f64
+// primitive tests in the reference's operation order at the leaves.  Distances and barycentrics of a hit are therefore
+// bit-identical to the reference's for the same primitive; only exact-t ties can resolve differently (tree order).
+// ANY = true: return at the first primitive other than `skip_prim` hit closer than tmax (shadow rays).
+template <bool ANY> __device__ __forceinline__ Hit64 trace_mixed(const DevScene &sc, D3v o, D3v d, double tmax, uint32_t skip_prim) {
+    Hit64 best;
+    best.prim = 0xFFFFFFFFu;
+    best.t = tmax; // +inf for closest-hit queries
+    best.bx = best.by = 0.0;
+    const float inf = __int_as_float(0x7f800000);
+    float tbound = ANY ? __double2float_ru(tmax) : inf;
+    const float ox = (float)o.x, oy = (float)o.y, oz = (float)o.z, dx = (float)d.x, dy = (float)d.y, dz = (float)d.z;
+    const float eps = 8.27180613e-25f;
+    const float idx = 1.0f / (fabsf(dx) > eps ? dx : copysignf(eps, dx));
+    const float idy = 1.0f / (fabsf(dy) > eps ? dy : copysignf(eps, dy));
+    const float idz = 1.0f / (fabsf(dz) > eps ? dz : copysignf(eps, dz));
+    const float oix = -ox * idx, oiy = -oy * idy, oiz = -oz * idz;
+    int32_t stack[PATHS_FAST_STACK];
+    int sp = 0;
+    int32_t node = sc.fast_root;
+    if (node == (int32_t)0x80000000) return best;
+    const float4 *__restrict__ nodes = sc.fast_nodes;
+    const float4 *__restrict__ leaves = sc.fast_leaves;
+    for (;;) {
+        while (node >= 0) {
+            const float4 n0 = __ldg(nodes + 4 * node), n1 = __ldg(nodes + 4 * node + 1), n2 = __ldg(nodes + 4 * node + 2), n3 = __ldg(nodes + 4 * node + 3);
+            // explicit fma: this translation unit is compiled with -fmad=false for the f64 reference arithmetic
+            float a0 = __fmaf_rn(n0.x, idx, oix), a1 = __fmaf_rn(n0.y, idx, oix), a2 = __fmaf_rn(n0.z, idy, oiy), a3 = __fmaf_rn(n0.w, idy, oiy);
+            float a4 = __fmaf_rn(n2.x, idz, oiz), a5 = __fmaf_rn(n2.y, idz, oiz);
+            float tn0 = fmaxf(fmaxf(fminf(a0, a1), fminf(a2, a3)), fmaxf(fminf(a4, a5), 0.0f));
+            float tf0 = fminf(fminf(fmaxf(a0, a1), fmaxf(a2, a3)), fminf(fmaxf(a4, a5), tbound)) * 1.0000004f;
+            float b0 = __fmaf_rn(n1.x, idx, oix), b1 = __fmaf_rn(n1.y, idx, oix), b2 = __fmaf_rn(n1.z, idy, oiy), b3 = __fmaf_rn(n1.w, idy, oiy);
+            float b4 = __fmaf_rn(n2.z, idz, oiz), b5 = __fmaf_rn(n2.w, idz, oiz);
+            float tn1 = fmaxf(fmaxf(fminf(b0, b1), fminf(b2, b3)), fmaxf(fminf(b4, b5), 0.0f));
+            float tf1 = fminf(fminf(fmaxf(b0, b1), fmaxf(b2, b3)), fminf(fmaxf(b4, b5), tbound)) * 1.0000004f;
+            bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
+            int32_t c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
+            if (h0 && h1) {
+                bool first0 = tn0 <= tn1;
+                node = first0 ? c0 : c1;
+                if (sp < PATHS_FAST_STACK) stack[sp++] = first0 ? c1 : c0;
+            } else if (h0) node = c0;
+            else if (h1) node = c1;
+            else {
+                if (sp == 0) return best;
+                node = stack[--sp];
+            }
+        }
+        {
+            uint32_t code = (uint32_t)~node;
+            uint32_t first = code >> 3, cnt = (code & 7u) + 1u;
+            for (uint32_t k = 0; k < cnt; k++) {
+                uint32_t prim = __float_as_uint(__ldg(leaves + 3 * (first + k) + 2).w) & 0x7FFFFFFFu;
+                if (ANY && prim == skip_prim) continue;
+                double t, bx, by;
+                if (prim_hit64(sc, prim, o, d, t, bx, by)) {
+                    // src/bvh.rs:93-104: the first hit is taken as it is (even t = inf), later ones only when strictly closer
+                    if (ANY ? t < best.t : (best.prim == 0xFFFFFFFFu || t < best.t)) {
+                        best.prim = prim;
+                        best.t = t;
+                        best.bx = bx;
+                        best.by = by;
+                        if (ANY) return best;
+                        tbound = __double2float_ru(t);
+                    }
+                }
+            }
+            if (sp == 0) return best;
+            node = stack[--sp];
+        }
+    }
+}
+
 // ------------------------------------------------------------------ resumable production traversal (persistent warps with lane refill)
 // The same arithmetic as trace_fast, cut into bounded steps so that a warp can hand a finished lane a new ray instead of
 // idling until its slowest ray ends (ncu on the batch-of-32 version: 7-9 of 32 threads active per instruction on bounce rays).

@@ -279,7 +279,7 @@ bool build_host_scene(const paths_scene_desc &desc, HostScene &out, std::string 
                                      std::fmax(std::fabs(out.bounds_lo.z), std::fabs(out.bounds_hi.z))));
     // The integrator offsets new ray origins by an absolute 1e-4 (src/trace.rs:57,89).  f32 origins keep that offset
     // meaningful while ulp(extent) is an order of magnitude below it: ulp(128) = 1.5e-5.
-    out.auto_precision = extent > 128.0 ? 64 : 32;
+    out.auto_precision = extent > 128.0 ? PATHS_PRECISION_MIXED : PATHS_PRECISION_F32;
     return true;
 }
 

@@ -10,6 +10,10 @@ paths_status trace_closest_f64(const SceneDevice *sd, const double *o, const dou
                                std::string &err) {
     return trace_closest_impl<double>(sd, o, d, n, prim, t, bary, err);
 }
+paths_status trace_closest_mixed(const SceneDevice *sd, const double *o, const double *d, size_t n, uint32_t *prim, double *t, double *bary,
+                                 std::string &err) {
+    return trace_closest_impl<double, true>(sd, o, d, n, prim, t, bary, err);
+}
 paths_status camera_rays_f64(const paths_camera &cam, int device, uint64_t seed, uint32_t sample, uint32_t x0, uint32_t y0, uint32_t w, uint32_t h,
                              double *o, double *d, double *weight, std::string &err) {
     return camera_rays_impl<double>(cam, device, seed, sample, x0, y0, w, h, o, d, weight, err);

@@ -20,6 +20,9 @@ namespace paths {
 #ifndef PATHS_LB_SHADE
 #define PATHS_LB_SHADE 5
 #endif
+#ifndef PATHS_LB_SHADE64
+#define PATHS_LB_SHADE64 4
+#endif
 #define PATHS_FLAG_SPECULAR 0x100u
 
 template <typename R> struct IsF64 {
@@ -71,7 +74,7 @@ __global__ void __launch_bounds__(256) k_raygen(DevCamera cam, uint32_t k0, uint
 }
 
 // ------------------------------------------------------------------ extend: closest hit (src/scene.rs:172-197 -> src/bvh.rs:78-140)
-template <typename R>
+template <typename R, bool MIXED>
 __global__ void __launch_bounds__(128) k_extend(DevScene sc, PathState<typename Vec4T<R>::type> ps, const uint32_t *queue, const uint32_t *count_ptr,
                                                 uint32_t *cursor) {
     const uint32_t count = *count_ptr;
@@ -84,7 +87,9 @@ __global__ void __launch_bounds__(128) k_extend(DevScene sc, PathState<typename 
             uint32_t slot = queue ? queue[i] : i;
             typename Vec4T<R>::type o = ps.ray_o[slot], d = ps.ray_d[slot];
             if constexpr (IsF64<R>::value) {
-                Hit64 h = trace_ref(sc, mk3((double)o.x, (double)o.y, (double)o.z), mk3((double)d.x, (double)d.y, (double)d.z));
+                Hit64 h = MIXED ? trace_mixed<false>(sc, mk3((double)o.x, (double)o.y, (double)o.z), mk3((double)d.x, (double)d.y, (double)d.z),
+                                                     (double)__int_as_float(0x7f800000), 0xFFFFFFFFu)
+                                : trace_ref(sc, mk3((double)o.x, (double)o.y, (double)o.z), mk3((double)d.x, (double)d.y, (double)d.z));
                 ps.hit[slot] = mk4(bits_to_real(h.prim, R(0)), R(h.t), R(h.bx), R(h.by));
             } else {
                 HitF h = trace_fast<false>(sc, (float)o.x, (float)o.y, (float)o.z, (float)d.x, (float)d.y, (float)d.z, __int_as_float(0x7f800000),
@@ -267,7 +272,7 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
 }
 
 template <typename R>
-__global__ void __launch_bounds__(128, (IsF64<R>::value ? 2 : PATHS_LB_SHADE)) k_shade(DevScene sc, PathState<typename Vec4T<R>::type> ps, ShardInfo shard, uint32_t s_base, uint32_t k0,
+__global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : PATHS_LB_SHADE)) k_shade(DevScene sc, PathState<typename Vec4T<R>::type> ps, ShardInfo shard, uint32_t s_base, uint32_t k0,
                                                uint32_t k1, uint32_t max_bounces, uint32_t ext, const uint32_t *queue, uint32_t *queue_next,
                                                const uint32_t *count_ptr, uint32_t *next_count, uint32_t *shadow_count, uint32_t *cursor,
                                                unsigned long long *totals) {
@@ -324,7 +329,7 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? 2 : PATHS_LB_SHADE)) k
 }
 
 // ------------------------------------------------------------------ shadow: visibility of the NEE sample (src/trace.rs:61-66)
-template <typename R>
+template <typename R, bool MIXED>
 __global__ void __launch_bounds__(128) k_shadow(DevScene sc, PathState<typename Vec4T<R>::type> ps, const uint32_t *count_ptr, uint32_t *cursor,
                                                 unsigned long long *totals) {
     typedef typename Vec4T<R>::type R4;
@@ -338,7 +343,19 @@ __global__ void __launch_bounds__(128) k_shadow(DevScene sc, PathState<typename 
             R4 o = ps.sh_o[i], d = ps.sh_d[i];
             uint32_t lid = real_to_bits(o.w), slot = real_to_bits(d.w);
             bool occluded;
-            if constexpr (IsF64<R>::value) {
+            if constexpr (IsF64<R>::value && MIXED) {
+                // any-hit over the production tree with f64 primitives: the same predicate as below, no rounding to f32
+                double t_light = (double)__int_as_float(0x7f800000);
+                uint32_t skip = 0xFFFFFFFFu;
+                D3v so = mk3((double)o.x, (double)o.y, (double)o.z), sdir = mk3((double)d.x, (double)d.y, (double)d.z);
+                if (lid != PATHS_LIGHT_ENV) {
+                    const DevLight &l = sc.lights[lid];
+                    skip = l.prim;
+                    double tl;
+                    if (l.geometry == 1 && sphere_hit64(mk3(l.v[0], l.v[1], l.v[2]), l.radius, so, sdir, tl)) t_light = tl;
+                }
+                occluded = trace_mixed<true>(sc, so, sdir, t_light, skip).prim != 0xFFFFFFFFu;
+            } else if constexpr (IsF64<R>::value) {
                 // the reference runs a full closest-hit query and compares entities (trace.rs:61-66)
                 Hit64 h = trace_ref(sc, mk3((double)o.x, (double)o.y, (double)o.z), mk3((double)d.x, (double)d.y, (double)d.z));
                 occluded = false;

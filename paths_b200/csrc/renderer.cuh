@@ -75,7 +75,7 @@ template <typename R> __global__ void k_add_sums(typename Vec4T<R>::type *sums, 
 }
 
 // ------------------------------------------------------------------ batch queries
-template <typename R>
+template <typename R, bool MIXED>
 __global__ void k_trace_closest(DevScene sc, const double *o, const double *d, uint32_t n, uint32_t *prim, double *t, double *bary) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -83,7 +83,8 @@ __global__ void k_trace_closest(DevScene sc, const double *o, const double *d, u
     uint32_t p;
     double tt, bx, by;
     if constexpr (IsF64<R>::value) {
-        Hit64 h = trace_ref(sc, mk3(ox, oy, oz), mk3(dx, dy, dz));
+        Hit64 h = MIXED ? trace_mixed<false>(sc, mk3(ox, oy, oz), mk3(dx, dy, dz), (double)__int_as_float(0x7f800000), 0xFFFFFFFFu)
+                        : trace_ref(sc, mk3(ox, oy, oz), mk3(dx, dy, dz));
         p = h.prim; tt = h.t; bx = h.bx; by = h.by;
     } else {
         HitF h = trace_fast<false>(sc, (float)ox, (float)oy, (float)oz, (float)dx, (float)dy, (float)dz, __int_as_float(0x7f800000), 0xFFFFFFFFu);
@@ -114,7 +115,7 @@ __global__ void k_camera_rays(DevCamera cam, uint32_t k0, uint32_t k1, uint32_t 
     weight[i] = wt;
 }
 
-template <typename R>
+template <typename R, bool MIXED = false>
 paths_status trace_closest_impl(const SceneDevice *sd, const double *o, const double *d, size_t n, uint32_t *prim, double *t, double *bary,
                                 std::string &err) {
     if (n == 0) return PATHS_OK;
@@ -134,7 +135,7 @@ paths_status trace_closest_impl(const SceneDevice *sd, const double *o, const do
         if (bary) PATHS_CU(cudaMalloc(&d_b, n * 24));
         PATHS_CU(cudaMemcpy(d_o, o, n * 24, cudaMemcpyHostToDevice));
         PATHS_CU(cudaMemcpy(d_d, d, n * 24, cudaMemcpyHostToDevice));
-        k_trace_closest<R><<<(unsigned)((n + 127) / 128), 128>>>(sd->view, d_o, d_d, (uint32_t)n, d_p, d_t, d_b);
+        k_trace_closest<R, MIXED><<<(unsigned)((n + 127) / 128), 128>>>(sd->view, d_o, d_d, (uint32_t)n, d_p, d_t, d_b);
         PATHS_CU(cudaGetLastError());
         PATHS_CU(cudaDeviceSynchronize());
         PATHS_CU(cudaMemcpy(prim, d_p, n * 4, cudaMemcpyDeviceToHost));

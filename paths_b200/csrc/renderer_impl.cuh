@@ -15,6 +15,7 @@ template <typename R> class RendererImpl : public RendererBase {
     cudaStream_t stream_ = nullptr;
     uint32_t W_, H_, npix_, n_local_ = 0, spp_pass_ = 1, n_ctl_ = 0;
     size_t n_slots_max_ = 0;
+    bool mixed_ = false;        // f64 instantiation over the production tree (PATHS_PRECISION_MIXED)
     uint32_t samples_done_ = 0; // global samples per pixel issued so far (all ranks together)
     int sm_count_ = 148, grid_trace_ = 0, grid_shade_ = 0, grid_stream_ = 0, variant_ = 3, grid4_ = 0, shade_variant_ = 1;
     size_t smem4_ = 0;
@@ -94,6 +95,7 @@ template <typename R> class RendererImpl : public RendererBase {
   public:
     RendererImpl(const SceneDevice *sd, const paths_camera &cam, const paths_render_opts &o) : sd_(sd), opts_(o) {
         cam_ = make_dev_camera(cam);
+        mixed_ = IsF64<R>::value && o.precision == PATHS_PRECISION_MIXED;
         W_ = cam.image_width;
         H_ = cam.image_height;
         npix_ = W_ * H_;
@@ -176,7 +178,7 @@ template <typename R> class RendererImpl : public RendererBase {
         if (const char *v = getenv("PATHS_SHADE_VARIANT")) shade_variant_ = atoi(v);
         // ---- persistent grids: every SM full
         int bps = 0;
-        if constexpr (IsF64<R>::value) PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_extend<R>, 128, 0));
+        if constexpr (IsF64<R>::value) PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (k_extend<R, false>), 128, 0));
         else PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_extend_refill<4, 16>, 128, 0));
         grid_trace_ = sm_count_ * std::max(bps, 1);
         PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_shade<R>, 128, 0));
@@ -231,7 +233,8 @@ template <typename R> class RendererImpl : public RendererBase {
             default: break;
             }
         }
-        k_extend<R><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, pc_.qcount + b, pc_.work + 3 * b);
+        if (mixed_) k_extend<R, true><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, pc_.qcount + b, pc_.work + 3 * b);
+        else k_extend<R, false><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, pc_.qcount + b, pc_.work + 3 * b);
     }
     void launch_shadow(uint32_t b) {
         if constexpr (!IsF64<R>::value) {
@@ -244,7 +247,8 @@ template <typename R> class RendererImpl : public RendererBase {
                 return;
             }
         }
-        k_shadow<R><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
+        if (mixed_) k_shadow<R, true><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
+        else k_shadow<R, false><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
     }
 
     paths_status run_pass(uint32_t s_base, uint32_t n_spp) { return run_pass_on(pixels_, n_local_, s_base, n_spp); }

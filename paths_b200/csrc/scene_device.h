@@ -60,6 +60,8 @@ paths_status trace_closest_f32(const SceneDevice *sd, const double *o, const dou
                                std::string &err);
 paths_status trace_closest_f64(const SceneDevice *sd, const double *o, const double *d, size_t n, uint32_t *prim, double *t, double *bary,
                                std::string &err);
+paths_status trace_closest_mixed(const SceneDevice *sd, const double *o, const double *d, size_t n, uint32_t *prim, double *t, double *bary,
+                                 std::string &err);
 paths_status camera_rays_f32(const paths_camera &cam, int device, uint64_t seed, uint32_t sample, uint32_t x0, uint32_t y0, uint32_t w, uint32_t h,
                              double *o, double *d, double *weight, std::string &err);
 paths_status camera_rays_f64(const paths_camera &cam, int device, uint64_t seed, uint32_t sample, uint32_t x0, uint32_t y0, uint32_t w, uint32_t h,

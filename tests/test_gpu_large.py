@@ -88,20 +88,52 @@ def test_dragon_image_f32(pb, oracle_mod):
     assert st["shadow_rays"] > 0 and st["bad_samples"] == 0
 
 
-def test_doom_auto_precision_is_f64_and_follows_oracle(pb, oracle_mod):
-    # coordinates +-700: the scene resolves to the f64 instantiation; per-vertex colours; big area light
+@pytest.mark.parametrize("precision", [0, 64])
+def test_doom_large_coordinates_follow_oracle_in_f64(pb, oracle_mod, precision):
+    # coordinates +-700: AUTO resolves to the mixed instantiation (f64 state, shading and primitive tests over the production tree);
+    # both it and the parity instantiation follow the oracle sample for sample.  Per-vertex colours; big area light.
     osc, cam = oracle_mod.load_scene("scenes/doom.yml", width=72, height=48)
     gsc = pb.Scene.load("scenes/doom.yml", width=72, height=48)
-    assert gsc.info["auto_precision"] == 64
-    r = pb.Renderer(cam, gsc, seed=6)  # PRECISION_AUTO
+    assert gsc.info["auto_precision"] == pb.PRECISION_MIXED == 48
+    r = pb.Renderer(cam, gsc, seed=6, precision=precision)
     _, _, eb = r.device_sums()
     assert eb == 8
     r.render_samples(3)
     s = r.sums()
+    st = r.stats()
     r.shutdown()
     sums, counts, ctr = osc.render(cam, 6, 0, 3)
     close = np.all(np.abs(s[..., :3] - sums) <= 1e-9 * (np.abs(sums) + 1e-3), axis=-1)
     assert close.mean() >= 0.995 and sums.max() > 0
+    assert st["shadow_rays"] > 0 and st["bad_samples"] == 0
+
+
+def test_mixed_fixed_rays_are_bit_exact_away_from_ties(pb, oracle_mod):
+    # production tree + the reference's f64 primitive tests: t and barycentrics bit-equal, ids equal unless two primitives tie exactly
+    for name, kw in (("doom", dict(width=240, height=160)), ("dragon", dict(width=240, height=160)), ("teapot", dict(width=240, height=160))):
+        osc, cam = oracle_mod.load_scene(f"scenes/{name}.yml", **kw)
+        gsc = pb.Scene.load(f"scenes/{name}.yml", **kw)
+        o, d, _ = oracle_mod.camera_rays(cam, 4, 0)
+        p0, t0, b0 = osc.trace_closest(o, d, want_bary=True)
+        p1, t1, b1 = gsc.find_intersection(o, d, precision=pb.PRECISION_MIXED, want_bary=True)
+        hit = p0 != oracle_mod.MISS
+        assert np.array_equal(hit, p1 != oracle_mod.MISS), name
+        assert np.array_equal(t0[hit], t1[hit]), name  # the closest distance itself never depends on the tree
+        same = p0 == p1
+        assert same.mean() > 0.9999, name
+        assert np.array_equal(b0[same & hit], b1[same & hit]), name
+        # incoherent rays off the surfaces
+        rng = np.random.default_rng(2)
+        sel = np.nonzero(hit)[0][:30000]
+        o2 = o[sel] + d[sel] * t0[sel, None]
+        d2 = rng.normal(size=o2.shape)
+        d2 /= np.linalg.norm(d2, axis=1, keepdims=True)
+        o2 += d2 * 1e-3
+        q0, s0 = osc.trace_closest(o2, d2)
+        q1, s1 = gsc.find_intersection(o2, d2, precision=pb.PRECISION_MIXED)
+        h2 = q0 != oracle_mod.MISS
+        assert np.array_equal(h2, q1 != oracle_mod.MISS) and np.array_equal(s0[h2], s1[h2]), name
+        assert (q0 == q1).mean() > 0.9999, name
 
 
 def test_environment_hdri_and_auto_material(pb, oracle_mod):
