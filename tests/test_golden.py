@@ -72,7 +72,7 @@ def test_oracle_reproduces_its_frozen_vectors(oracle_mod, vec):
         osc, cam = oracle_mod.load_scene(f"scenes/{name}.yml", width=w, height=h)
         o, d, wt = oracle_mod.camera_rays(cam, 9, 0)
         assert np.array_equal(o, vec[f"{name}.rays_o"]) and np.array_equal(d, vec[f"{name}.rays_d"]) and np.array_equal(wt, vec[f"{name}.rays_w"])
-        p, t, b = osc.trace_closest(o, d, want_bary=True)
+        p, t, b = osc.trace_closest(vec[f"{name}.fixed_o"], vec[f"{name}.fixed_d"], want_bary=True)
         assert np.array_equal(p, vec[f"{name}.prim"]) and np.array_equal(t, vec[f"{name}.t"]) and np.array_equal(b, vec[f"{name}.bary"])
         p2, t2 = osc.trace_closest(vec[f"{name}.rays2_o"], vec[f"{name}.rays2_d"])
         assert np.array_equal(p2, vec[f"{name}.prim2"]) and np.array_equal(t2, vec[f"{name}.t2"])
@@ -92,7 +92,7 @@ def test_cuda_path_reproduces_the_frozen_vectors(name, w, h, vec):
     o, d, wt = pb.camera_rays(sc.camera, 9, 0, precision=64)
     assert np.allclose(o, vec[f"{name}.rays_o"], rtol=0, atol=1e-12) and np.allclose(d, vec[f"{name}.rays_d"], rtol=0, atol=1e-12)
     miss = 0xFFFFFFFF
-    for rays_o, rays_d, kp, kt in ((f"{name}.rays_o", f"{name}.rays_d", f"{name}.prim", f"{name}.t"),
+    for rays_o, rays_d, kp, kt in ((f"{name}.fixed_o", f"{name}.fixed_d", f"{name}.prim", f"{name}.t"),
                                    (f"{name}.rays2_o", f"{name}.rays2_d", f"{name}.prim2", f"{name}.t2")):
         ro, rd, p0, t0 = vec[rays_o], vec[rays_d], vec[kp], vec[kt]
         hit = p0 != miss

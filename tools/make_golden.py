@@ -64,8 +64,11 @@ def main():
     for name, w, h in SCENES:
         osc, cam = oracle.load_scene(str(ROOT / "scenes" / f"{name}.yml"), width=w, height=h)
         o, d, wt = oracle.camera_rays(cam, 9, 0)
-        p, t, b = osc.trace_closest(o, d, want_bary=True)
         v[f"{name}.rays_o"], v[f"{name}.rays_d"], v[f"{name}.rays_w"] = o, d, wt
+        # fixed rays for the traversal checks are stored f32-representable, so that every instantiation sees the same ray
+        o, d = o.astype(np.float32).astype(np.float64), d.astype(np.float32).astype(np.float64)
+        p, t, b = osc.trace_closest(o, d, want_bary=True)
+        v[f"{name}.fixed_o"], v[f"{name}.fixed_d"] = o, d
         v[f"{name}.prim"], v[f"{name}.t"], v[f"{name}.bary"] = p, t, b
         # bounce rays: leave every hit point in a seeded random direction
         rng = np.random.default_rng(3)
@@ -74,6 +77,7 @@ def main():
         d2 = rng.normal(size=o2.shape)
         d2 /= np.linalg.norm(d2, axis=1, keepdims=True)
         o2 = o2 + d2 * 1e-3
+        o2, d2 = o2.astype(np.float32).astype(np.float64), d2.astype(np.float32).astype(np.float64)
         p2, t2 = osc.trace_closest(o2, d2)
         v[f"{name}.rays2_o"], v[f"{name}.rays2_d"], v[f"{name}.prim2"], v[f"{name}.t2"] = o2, d2, p2, t2
         sums, counts, _ = osc.render(cam, 5, 0, 3)
