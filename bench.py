@@ -279,7 +279,7 @@ def run_ours(args, rank, world, local_rank):
                 dist.reduce(frame, dst=0, op=dist.ReduceOp.SUM)
                 if rank == 0:
                     sums.copy_(frame)                 # the combined estimator is what gets tonemapped
-            re_.sync()
+            re_.drain_result_queue()
         if rank == 0:
             pb.check(pb.lib().paths_renderer_image_rgb24(re_._h, out.ctypes.data))  # device -> host: tonemapped frame
 

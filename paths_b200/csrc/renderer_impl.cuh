@@ -29,6 +29,8 @@ template <typename R> class RendererImpl : public RendererBase {
     PathState<R4> ps_;
     PassControl pc_;
     uint32_t *ctl_block_ = nullptr;
+    void *stage_ = nullptr; // staging buffer of the image / estimator transfers
+    size_t stage_bytes_ = 0;
     std::vector<void *> allocs_;
     // stats
     paths_stats stats_;
@@ -116,6 +118,7 @@ template <typename R> class RendererImpl : public RendererBase {
         }
         for (cudaEvent_t e : pool_) cudaEventDestroy(e);
         for (void *p : allocs_) cudaFree(p);
+        if (stage_) cudaFree(stage_);
         if (stream_) cudaStreamDestroy(stream_);
     }
 
@@ -153,7 +156,7 @@ template <typename R> class RendererImpl : public RendererBase {
             return PATHS_ERR_INVALID_ARG;
         }
         if (alloc(&sums_, npix_) != PATHS_OK) return PATHS_ERR_CUDA;
-        PATHS_CU(cudaMemset(sums_, 0, (size_t)npix_ * sizeof(R4)));
+        PATHS_CU(cudaMemsetAsync(sums_, 0, (size_t)npix_ * sizeof(R4), stream_));
         R4 **state[] = {&ps_.ray_o, &ps_.ray_d, &ps_.hit, &ps_.thr, &ps_.col};
         for (R4 **p : state)
             if (alloc(p, n_slots_max_) != PATHS_OK) return PATHS_ERR_CUDA;
@@ -170,7 +173,7 @@ template <typename R> class RendererImpl : public RendererBase {
         pc_.scount = ctl_block_ + nb;
         pc_.work = ctl_block_ + 2 * nb;
         if (alloc(&pc_.totals, 4) != PATHS_OK) return PATHS_ERR_CUDA;
-        PATHS_CU(cudaMemset(pc_.totals, 0, 4 * sizeof(unsigned long long)));
+        PATHS_CU(cudaMemsetAsync(pc_.totals, 0, 4 * sizeof(unsigned long long), stream_));
         // traversal kernel: two-wide nodes + local stack for small (L1-resident) scenes, four-wide nodes + shared-memory stack
         // above 64k primitives (measured: teapot 7.5 vs 7.8 ms, dragon 25.4 vs 24.4 ms per 16 spp; profiles/r01_*)
         variant_ = sd_->view.n_prims > 65536u ? 16 : 3;
@@ -325,50 +328,53 @@ template <typename R> class RendererImpl : public RendererBase {
         resolve_timers();
         return PATHS_OK;
     }
+    // one staging buffer for every image / estimator transfer, grown on demand (no cudaMalloc / cudaFree per frame: both
+    // synchronise the whole device, which costs tens of milliseconds once NCCL communicators are alive)
+    paths_status staging(size_t bytes, void **out) {
+        if (bytes > stage_bytes_) {
+            if (stage_) cudaFree(stage_);
+            stage_ = nullptr;
+            stage_bytes_ = 0;
+            PATHS_CU(cudaMalloc(&stage_, bytes));
+            stage_bytes_ = bytes;
+        }
+        *out = stage_;
+        return PATHS_OK;
+    }
     paths_status image_f32(float *rgb) override {
         PATHS_CU(cudaSetDevice(sd_->device));
         float *d = nullptr;
-        PATHS_CU(cudaMalloc(&d, (size_t)npix_ * 12));
+        if (staging((size_t)npix_ * 12, (void **)&d) != PATHS_OK) return PATHS_ERR_CUDA;
         k_image_f32<R><<<(npix_ + 255) / 256, 256, 0, stream_>>>(sums_, npix_, W_, d);
-        cudaError_t e = cudaMemcpyAsync(rgb, d, (size_t)npix_ * 12, cudaMemcpyDeviceToHost, stream_);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(stream_);
-        cudaFree(d);
-        PATHS_CU(e);
+        PATHS_CU(cudaMemcpyAsync(rgb, d, (size_t)npix_ * 12, cudaMemcpyDeviceToHost, stream_));
+        PATHS_CU(cudaStreamSynchronize(stream_));
         return PATHS_OK;
     }
     paths_status image_rgb24(uint8_t *rgb) override {
         PATHS_CU(cudaSetDevice(sd_->device));
         uint8_t *d = nullptr;
-        PATHS_CU(cudaMalloc(&d, (size_t)npix_ * 3));
+        if (staging((size_t)npix_ * 3, (void **)&d) != PATHS_OK) return PATHS_ERR_CUDA;
         k_image_rgb24<R><<<(npix_ + 255) / 256, 256, 0, stream_>>>(sums_, npix_, W_, d);
-        cudaError_t e = cudaMemcpyAsync(rgb, d, (size_t)npix_ * 3, cudaMemcpyDeviceToHost, stream_);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(stream_);
-        cudaFree(d);
-        PATHS_CU(e);
+        PATHS_CU(cudaMemcpyAsync(rgb, d, (size_t)npix_ * 3, cudaMemcpyDeviceToHost, stream_));
+        PATHS_CU(cudaStreamSynchronize(stream_));
         return PATHS_OK;
     }
     paths_status get_sums(double *sums4) override {
         PATHS_CU(cudaSetDevice(sd_->device));
         double4 *d = nullptr;
-        PATHS_CU(cudaMalloc(&d, (size_t)npix_ * 32));
+        if (staging((size_t)npix_ * 32, (void **)&d) != PATHS_OK) return PATHS_ERR_CUDA;
         k_sums_to_f64<R><<<(npix_ + 255) / 256, 256, 0, stream_>>>(sums_, npix_, d);
-        cudaError_t e = cudaMemcpyAsync(sums4, d, (size_t)npix_ * 32, cudaMemcpyDeviceToHost, stream_);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(stream_);
-        cudaFree(d);
-        PATHS_CU(e);
+        PATHS_CU(cudaMemcpyAsync(sums4, d, (size_t)npix_ * 32, cudaMemcpyDeviceToHost, stream_));
+        PATHS_CU(cudaStreamSynchronize(stream_));
         return PATHS_OK;
     }
     paths_status add_sums(const double *sums4) override {
         PATHS_CU(cudaSetDevice(sd_->device));
         double4 *d = nullptr;
-        PATHS_CU(cudaMalloc(&d, (size_t)npix_ * 32));
-        cudaError_t e = cudaMemcpyAsync(d, sums4, (size_t)npix_ * 32, cudaMemcpyHostToDevice, stream_);
-        if (e == cudaSuccess) {
-            k_add_sums<R><<<(npix_ + 255) / 256, 256, 0, stream_>>>(sums_, npix_, d);
-            e = cudaStreamSynchronize(stream_);
-        }
-        cudaFree(d);
-        PATHS_CU(e);
+        if (staging((size_t)npix_ * 32, (void **)&d) != PATHS_OK) return PATHS_ERR_CUDA;
+        PATHS_CU(cudaMemcpyAsync(d, sums4, (size_t)npix_ * 32, cudaMemcpyHostToDevice, stream_));
+        k_add_sums<R><<<(npix_ + 255) / 256, 256, 0, stream_>>>(sums_, npix_, d);
+        PATHS_CU(cudaStreamSynchronize(stream_));
         return PATHS_OK;
     }
     paths_status device_sums(void **ptr, size_t *n, int32_t *elem_bytes) override {
@@ -402,8 +408,8 @@ template <typename R> class RendererImpl : public RendererBase {
     paths_status reset() override { // renderer.rs:122-128,143-150: a new epoch drops the estimator
         PATHS_CU(cudaSetDevice(sd_->device));
         PATHS_CU(cudaStreamSynchronize(stream_));
-        PATHS_CU(cudaMemset(sums_, 0, (size_t)npix_ * sizeof(R4)));
-        PATHS_CU(cudaMemset(pc_.totals, 0, 4 * sizeof(unsigned long long)));
+        PATHS_CU(cudaMemsetAsync(sums_, 0, (size_t)npix_ * sizeof(R4), stream_));
+        PATHS_CU(cudaMemsetAsync(pc_.totals, 0, 4 * sizeof(unsigned long long), stream_));
         samples_done_ = 0;
         sweep_pos_ = 0;
         n_previews_ = 0;
