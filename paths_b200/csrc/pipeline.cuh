@@ -864,9 +864,9 @@ template <typename R> __global__ void k_tally(PassControl pc, uint32_t n_bounces
             e += pc.qcount[b];
             s += pc.scount[b];
         }
-        pc.totals[0] += e;
-        pc.totals[1] += s;
-        pc.totals[3] += n_slots;
+        atomicAdd(pc.totals + 0, e); // two pass contexts may tally at the same time
+        atomicAdd(pc.totals + 1, s);
+        atomicAdd(pc.totals + 3, (unsigned long long)n_slots);
     }
 }
 

@@ -12,7 +12,28 @@ template <typename R> class RendererImpl : public RendererBase {
     const SceneDevice *sd_;
     paths_render_opts opts_;
     DevCamera cam_;
-    cudaStream_t stream_ = nullptr;
+    cudaStream_t stream_ = nullptr; // the renderer's stream: everything a caller can observe is ordered on it
+    // Two pass contexts on two streams: consecutive passes of one render() call overlap, so that the thin late bounces of one pass
+    // (and the drain of every persistent kernel) run next to the wide early bounces of the other.  Accumulation stays in pass order.
+    struct PassCtx {
+        PathState<R4> ps;
+        PassControl pc;
+        uint32_t *ctl = nullptr;
+        cudaStream_t stream = nullptr;
+        cudaEvent_t acc = nullptr; // recorded after this context's last k_accumulate
+        bool acc_valid = false;
+    };
+    PassCtx ctx_[4];
+    int n_ctx_ = 1, cur_ = 0, next_ctx_ = 0;
+    cudaStream_t cs_ = nullptr; // stream of the context in use
+    cudaEvent_t fork_ = nullptr, join_ = nullptr;
+    void use_ctx(int i) {
+        cur_ = i;
+        ps_ = ctx_[i].ps;
+        pc_ = ctx_[i].pc;
+        ctl_block_ = ctx_[i].ctl;
+        cs_ = ctx_[i].stream;
+    }
     uint32_t W_, H_, npix_, n_local_ = 0, spp_pass_ = 1, n_ctl_ = 0;
     size_t n_slots_max_ = 0;
     bool mixed_ = false;        // f64 instantiation over the production tree (PATHS_PRECISION_MIXED)
@@ -65,13 +86,13 @@ template <typename R> class RendererImpl : public RendererBase {
         t.a = get_event();
         t.b = get_event();
         t.cls = cls;
-        cudaEventRecord(t.a, stream_);
+        cudaEventRecord(t.a, cs_);
         timed_.push_back(t);
     }
     void toc() {
         stats_.kernel_launches++;
         if (!opts_.time_kernels) return;
-        cudaEventRecord(timed_.back().b, stream_);
+        cudaEventRecord(timed_.back().b, cs_);
     }
     void resolve_timers() {
         for (Timed &t : timed_) {
@@ -119,6 +140,15 @@ template <typename R> class RendererImpl : public RendererBase {
         for (cudaEvent_t e : pool_) cudaEventDestroy(e);
         for (void *p : allocs_) cudaFree(p);
         if (stage_) cudaFree(stage_);
+        for (int c = 1; c < 4; c++)
+            if (ctx_[c].stream) {
+                cudaStreamSynchronize(ctx_[c].stream);
+                cudaStreamDestroy(ctx_[c].stream);
+            }
+        for (PassCtx &c : ctx_)
+            if (c.acc) cudaEventDestroy(c.acc);
+        if (fork_) cudaEventDestroy(fork_);
+        if (join_) cudaEventDestroy(join_);
         if (stream_) cudaStreamDestroy(stream_);
     }
 
@@ -157,23 +187,39 @@ template <typename R> class RendererImpl : public RendererBase {
         }
         if (alloc(&sums_, npix_) != PATHS_OK) return PATHS_ERR_CUDA;
         PATHS_CU(cudaMemsetAsync(sums_, 0, (size_t)npix_ * sizeof(R4), stream_));
-        R4 **state[] = {&ps_.ray_o, &ps_.ray_d, &ps_.hit, &ps_.thr, &ps_.col};
-        for (R4 **p : state)
-            if (alloc(p, n_slots_max_) != PATHS_OK) return PATHS_ERR_CUDA;
-        // shadow records: one per path and bounce for light NEE, one more with environment NEE
-        size_t n_shadow = n_slots_max_ * ((opts_.extensions & PATHS_EXT_ENV_NEE) ? 2 : 1);
-        R4 **shadow[] = {&ps_.sh_o, &ps_.sh_d, &ps_.sh_c};
-        for (R4 **p : shadow)
-            if (alloc(p, n_shadow) != PATHS_OK) return PATHS_ERR_CUDA;
-        if (alloc(&pc_.queue[0], n_slots_max_) != PATHS_OK || alloc(&pc_.queue[1], n_slots_max_) != PATHS_OK) return PATHS_ERR_CUDA;
-        uint32_t nb = opts_.max_bounces + 2;
+        // pass contexts: the second one only when kernels are not timed one by one (overlap would blur per-kernel times)
+        n_ctx_ = opts_.time_kernels ? 1 : 2;
+        if (const char *v = getenv("PATHS_PIPELINE")) n_ctx_ = opts_.time_kernels ? 1 : std::min(4, std::max(1, atoi(v))); // development switch
+        unsigned long long *totals = nullptr;
+        if (alloc(&totals, 4) != PATHS_OK) return PATHS_ERR_CUDA;
+        PATHS_CU(cudaMemsetAsync(totals, 0, 4 * sizeof(unsigned long long), stream_));
+        const uint32_t nb = opts_.max_bounces + 2;
         n_ctl_ = 5 * nb;
-        if (alloc(&ctl_block_, n_ctl_) != PATHS_OK) return PATHS_ERR_CUDA;
-        pc_.qcount = ctl_block_;
-        pc_.scount = ctl_block_ + nb;
-        pc_.work = ctl_block_ + 2 * nb;
-        if (alloc(&pc_.totals, 4) != PATHS_OK) return PATHS_ERR_CUDA;
-        PATHS_CU(cudaMemsetAsync(pc_.totals, 0, 4 * sizeof(unsigned long long), stream_));
+        for (int c = 0; c < n_ctx_; c++) {
+            PassCtx &x = ctx_[c];
+            std::memset(&x.ps, 0, sizeof(x.ps));
+            std::memset(&x.pc, 0, sizeof(x.pc));
+            R4 **state[] = {&x.ps.ray_o, &x.ps.ray_d, &x.ps.hit, &x.ps.thr, &x.ps.col};
+            for (R4 **p : state)
+                if (alloc(p, n_slots_max_) != PATHS_OK) return PATHS_ERR_CUDA;
+            // shadow records: one per path and bounce for light NEE, one more with environment NEE
+            size_t n_shadow = n_slots_max_ * ((opts_.extensions & PATHS_EXT_ENV_NEE) ? 2 : 1);
+            R4 **shadow[] = {&x.ps.sh_o, &x.ps.sh_d, &x.ps.sh_c};
+            for (R4 **p : shadow)
+                if (alloc(p, n_shadow) != PATHS_OK) return PATHS_ERR_CUDA;
+            if (alloc(&x.pc.queue[0], n_slots_max_) != PATHS_OK || alloc(&x.pc.queue[1], n_slots_max_) != PATHS_OK) return PATHS_ERR_CUDA;
+            if (alloc(&x.ctl, n_ctl_) != PATHS_OK) return PATHS_ERR_CUDA;
+            x.pc.qcount = x.ctl;
+            x.pc.scount = x.ctl + nb;
+            x.pc.work = x.ctl + 2 * nb;
+            x.pc.totals = totals;
+            if (c == 0) x.stream = stream_;
+            else PATHS_CU(cudaStreamCreateWithFlags(&x.stream, cudaStreamNonBlocking));
+            PATHS_CU(cudaEventCreateWithFlags(&x.acc, cudaEventDisableTiming));
+        }
+        PATHS_CU(cudaEventCreateWithFlags(&fork_, cudaEventDisableTiming));
+        PATHS_CU(cudaEventCreateWithFlags(&join_, cudaEventDisableTiming));
+        use_ctx(0);
         // traversal kernel: two-wide nodes + local stack for small (L1-resident) scenes, four-wide nodes + shared-memory stack
         // above 64k primitives (measured: teapot 7.5 vs 7.8 ms, dragon 25.4 vs 24.4 ms per 16 spp; profiles/r01_*)
         variant_ = sd_->view.n_prims > 65536u ? 16 : 3;
@@ -213,45 +259,45 @@ template <typename R> class RendererImpl : public RendererBase {
             const uint32_t *cnt = pc_.qcount + b;
             uint32_t *cur = pc_.work + 3 * b;
             switch (variant_) {
-            case 1: k_extend_refill<4, 8><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 2: k_extend_refill<8, 8><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 3: k_extend_refill<4, 16><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 4: k_extend_refill<2, 4><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 5: k_extend_refill<1, 1><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 6: k_extend_spec<4, 16, 3><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 7: k_extend_spec<4, 16, 4><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 8: k_extend_spec<2, 16, 6><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 9: k_extend_spec<4, 8, 2><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 10: k_extend4<4, 16, 2><<<grid4_, 128, smem4_, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 11: k_extend4<4, 16, 1><<<grid4_, 128, smem4_, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 12: k_extend4<2, 16, 3><<<grid4_, 128, smem4_, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 13: k_extend4s<2, 16, 8, 8><<<grid4_, 128, smem4_, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 14: k_extend4s<2, 16, 16, 12><<<grid4_, 128, smem4_, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 15: k_extend4s<4, 16, 8, 16><<<grid4_, 128, smem4_, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 16: k_extend4s<1, 8, 16, 8><<<grid4_, 128, smem4_, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 20: k_extend2s<2, 16, 8, 8><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 21: k_extend2s<2, 16, 16, 12><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 22: k_extend2s<4, 16, 8, 16><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 23: k_extend2s<1, 8, 16, 8><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 1: k_extend_refill<4, 8><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 2: k_extend_refill<8, 8><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 3: k_extend_refill<4, 16><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 4: k_extend_refill<2, 4><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 5: k_extend_refill<1, 1><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 6: k_extend_spec<4, 16, 3><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 7: k_extend_spec<4, 16, 4><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 8: k_extend_spec<2, 16, 6><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 9: k_extend_spec<4, 8, 2><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 10: k_extend4<4, 16, 2><<<grid4_, 128, smem4_, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 11: k_extend4<4, 16, 1><<<grid4_, 128, smem4_, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 12: k_extend4<2, 16, 3><<<grid4_, 128, smem4_, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 13: k_extend4s<2, 16, 8, 8><<<grid4_, 128, smem4_, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 14: k_extend4s<2, 16, 16, 12><<<grid4_, 128, smem4_, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 15: k_extend4s<4, 16, 8, 16><<<grid4_, 128, smem4_, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 16: k_extend4s<1, 8, 16, 8><<<grid4_, 128, smem4_, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 20: k_extend2s<2, 16, 8, 8><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 21: k_extend2s<2, 16, 16, 12><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 22: k_extend2s<4, 16, 8, 16><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 23: k_extend2s<1, 8, 16, 8><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
             default: break;
             }
         }
-        if (mixed_) k_extend<R, true><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, pc_.qcount + b, pc_.work + 3 * b);
-        else k_extend<R, false><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, q, pc_.qcount + b, pc_.work + 3 * b);
+        if (mixed_) k_extend<R, true><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, pc_.qcount + b, pc_.work + 3 * b);
+        else k_extend<R, false><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, pc_.qcount + b, pc_.work + 3 * b);
     }
     void launch_shadow(uint32_t b) {
         if constexpr (!IsF64<R>::value) {
             if (variant_ >= 10 && variant_ < 20) {
-                k_shadow4<4, 16, 2><<<grid4_, 128, smem4_, stream_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
+                k_shadow4<4, 16, 2><<<grid4_, 128, smem4_, cs_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
                 return;
             }
             if (variant_ != 0) {
-                k_shadow_refill<4, 8><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
+                k_shadow_refill<4, 8><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
                 return;
             }
         }
-        if (mixed_) k_shadow<R, true><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
-        else k_shadow<R, false><<<grid_trace_, 128, 0, stream_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
+        if (mixed_) k_shadow<R, true><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
+        else k_shadow<R, false><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
     }
 
     paths_status run_pass(uint32_t s_base, uint32_t n_spp) { return run_pass_on(pixels_, n_local_, s_base, n_spp); }
@@ -266,9 +312,9 @@ template <typename R> class RendererImpl : public RendererBase {
         shard.pixels = pixels;
         shard.n_local_magic = n_local > 1 ? (uint32_t)((1ull << 32) / n_local) : 0xFFFFFFFFu;
         const uint32_t nb = opts_.max_bounces + 1; // segments per path (trace.rs:13-16)
-        PATHS_CU(cudaMemsetAsync(ctl_block_, 0, n_ctl_ * sizeof(uint32_t), stream_));
+        PATHS_CU(cudaMemsetAsync(ctl_block_, 0, n_ctl_ * sizeof(uint32_t), cs_));
         tic(0);
-        k_raygen<R><<<grid_stream_, 256, 0, stream_>>>(cam_, k0, k1, shard, s_base, n_slots, ps_, pc_);
+        k_raygen<R><<<grid_stream_, 256, 0, cs_>>>(cam_, k0, k1, shard, s_base, n_slots, ps_, pc_);
         toc();
         for (uint32_t b = 0; b < nb; b++) {
             const uint32_t *q = b == 0 ? nullptr : pc_.queue[b & 1];
@@ -277,7 +323,7 @@ template <typename R> class RendererImpl : public RendererBase {
             toc();
             stats_.n_extend_launches++;
             tic(2);
-            k_shade<R><<<grid_shade_, 128, 0, stream_>>>(sd_->view, ps_, shard, s_base, k0, k1, opts_.max_bounces, opts_.extensions, q,
+            k_shade<R><<<grid_shade_, 128, 0, cs_>>>(sd_->view, ps_, shard, s_base, k0, k1, opts_.max_bounces, opts_.extensions, q,
                                                         pc_.queue[(b + 1) & 1],
                                                         pc_.qcount + b, pc_.qcount + b + 1, pc_.scount + b, shade_variant_ == 1 ? nullptr : pc_.work + 3 * b + 1, pc_.totals);
             toc();
@@ -289,9 +335,9 @@ template <typename R> class RendererImpl : public RendererBase {
             }
         }
         tic(4);
-        k_accumulate<R><<<grid_stream_, 256, 0, stream_>>>(ps_, shard, n_spp, sums_);
+        k_accumulate<R><<<grid_stream_, 256, 0, cs_>>>(ps_, shard, n_spp, sums_);
         toc();
-        k_tally<R><<<1, 32, 0, stream_>>>(pc_, nb, n_slots);
+        k_tally<R><<<1, 32, 0, cs_>>>(pc_, nb, n_slots);
         stats_.kernel_launches++;
         stats_.passes++;
         PATHS_CU(cudaGetLastError());
@@ -313,9 +359,27 @@ template <typename R> class RendererImpl : public RendererBase {
         }
         cudaEvent_t ea = get_event(), eb = get_event();
         cudaEventRecord(ea, stream_);
+        const bool overlap = n_ctx_ > 1 && s1 - s0 > spp_pass_;
+        if (overlap) { // work already queued on the renderer's stream (a reset, a caller's copy) comes first on both streams
+            PATHS_CU(cudaEventRecord(fork_, stream_));
+            for (int c = 1; c < n_ctx_; c++) PATHS_CU(cudaStreamWaitEvent(ctx_[c].stream, fork_, 0));
+        }
+        // passes go round the contexts; the round continues across calls so that accumulation order stays pass order
         for (uint32_t s = s0; s < s1; s += spp_pass_) {
+            use_ctx(overlap ? next_ctx_ : 0);
+            if (overlap) next_ctx_ = (next_ctx_ + 1) % n_ctx_;
             paths_status st = run_pass(s, std::min(spp_pass_, s1 - s));
-            if (st != PATHS_OK) return st;
+            if (st != PATHS_OK) {
+                use_ctx(0);
+                return st;
+            }
+        }
+        use_ctx(0);
+        if (overlap) { // join: whatever follows on the renderer's stream sees every pass
+            for (int c = 1; c < n_ctx_; c++) {
+                PATHS_CU(cudaEventRecord(join_, ctx_[c].stream));
+                PATHS_CU(cudaStreamWaitEvent(stream_, join_, 0));
+            }
         }
         cudaEventRecord(eb, stream_);
         spans_.push_back(std::make_pair(ea, eb));
