@@ -188,7 +188,7 @@ def run_ours(args, rank, world, local_rank):
 
     def make_renderer(timed):
         return pb.Renderer(scene.camera, scene, device=local_rank, precision=args.precision, seed=args.seed, rank=rank, world=world,
-                           shard_mode=pb.SHARD_SAMPLES, time_kernels=timed)
+                           shard_mode=pb.SHARD_TILES if args.shard == "tiles" else pb.SHARD_SAMPLES, time_kernels=timed)
 
     def barrier():
         if world > 1:
@@ -203,7 +203,9 @@ def run_ours(args, rank, world, local_rank):
         frame = torch.empty_like(sums) if world > 1 else None
 
         def step():
-            r.render_samples(S * world, wait=False)  # this rank renders its S-sample share of the frame increment
+            # sample shards: this rank renders its S-sample share of the S * world samples of every pixel; tile shards: all S * world
+            # samples of its own 1/world of the pixels -- S x W x H camera paths per GPU per step either way (weak scaling)
+            r.render_samples(S * world, wait=False)
             if world > 1:
                 frame.copy_(sums)
                 dist.reduce(frame, dst=0, op=dist.ReduceOp.SUM)  # partial radiance buffers -> rank 0 over NVLink
@@ -324,7 +326,8 @@ def run_ours(args, rank, world, local_rank):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32" if (args.precision or info["auto_precision"]) == 32 else "f64", "data": "synthetic",
-            "config": {"workload": f"{yaml} at {W}x{H}, {S} spp per GPU per step, sample-range sharding, NCCL reduce of the float4 buffer per step"
+            "config": {"workload": f"{yaml} at {W}x{H}, {S} spp per GPU per step, " + ("64x64-tile" if args.shard == "tiles" else "sample-range")
+                                   + " sharding, NCCL reduce of the float4 buffer per step"
                        if world > 1 else f"{yaml} at {W}x{H}, {S} spp per step", "scene": args.scene, "width": W, "height": H,
                        "spp_per_step_per_gpu": S, "prims": info["n_prims"], "seed": args.seed,
                        "l2": "per-pass path state (8.3M slots x 136 B = 1.1 GB) streams through HBM and exceeds the 126 MB L2; the scene tables "
@@ -361,6 +364,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--scene", default="teapot", choices=sorted(SCENES))
     ap.add_argument("--spp-step", type=int, default=64)
+    ap.add_argument("--shard", default="samples", choices=["samples", "tiles"],
+                    help="N > 1: each GPU renders a sample range of every pixel (default) or all samples of its 64x64 tiles")
     ap.add_argument("--precision", type=int, default=0, choices=[0, 32, 64])
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for the cpu_baseline leg")
