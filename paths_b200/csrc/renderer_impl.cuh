@@ -334,9 +334,16 @@ template <typename R> class RendererImpl : public RendererBase {
                 stats_.n_shadow_launches++;
             }
         }
+        // the estimator is shared by the pass contexts: accumulate in pass order (the previous pass ran on the previous context)
+        if (n_ctx_ > 1 && ctx_[(cur_ + n_ctx_ - 1) % n_ctx_].acc_valid)
+            PATHS_CU(cudaStreamWaitEvent(cs_, ctx_[(cur_ + n_ctx_ - 1) % n_ctx_].acc, 0));
         tic(4);
         k_accumulate<R><<<grid_stream_, 256, 0, cs_>>>(ps_, shard, n_spp, sums_);
         toc();
+        if (n_ctx_ > 1) {
+            PATHS_CU(cudaEventRecord(ctx_[cur_].acc, cs_));
+            ctx_[cur_].acc_valid = true;
+        }
         k_tally<R><<<1, 32, 0, cs_>>>(pc_, nb, n_slots);
         stats_.kernel_launches++;
         stats_.passes++;

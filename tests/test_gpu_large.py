@@ -154,3 +154,43 @@ def test_environment_hdri_and_auto_material(pb, oracle_mod):
     a = osc.render(cam, 8, 0, 16)[0] / 16
     b = osc.render(cam, 9, 0, 16)[0] / 16
     assert relrmse(g, a) <= 0.5 * relrmse(a, b)
+
+
+def test_full_size_properties_teapot_1080p(pb):
+    # BASELINE's headline size, through properties that need no oracle run: the estimator is a pure function of (seed, pixel, sample),
+    # whatever the launch order, pass size, number of pass contexts, shard layout or call pattern
+    sc = pb.Scene.load("scenes/teapot.yml", width=1920, height=1080)
+
+    def sums(spp_calls, **kw):
+        r = pb.Renderer(sc.camera, sc, precision=32, seed=21, **kw)
+        for n in spp_calls:
+            r.render_samples(n)
+        s = r.sums()
+        st = r.stats()
+        r.shutdown()
+        return s, st
+
+    a, st = sums([20])
+    assert st["samples"] == 20 * 1920 * 1080 and st["bad_samples"] == 0
+    assert np.all(a[..., 3] == 20) and np.isfinite(a).all() and a[..., :3].min() >= 0
+    b, _ = sums([20])
+    assert np.array_equal(a, b)                      # run to run
+    c, _ = sums([3, 1, 16])
+    assert np.array_equal(a, c)                      # additivity over calls: render(3) + render(1) + render(16) == render(20)
+    d, _ = sums([20], samples_per_pass=3)
+    assert np.array_equal(a, d)                      # pass size (7 passes instead of 2)
+    # shards: 3 ranks by tiles are disjoint and bit-identical; 3 ranks by sample ranges sum to the same image up to f32 rounding
+    tiles = [sums([20], rank=k, world=3, shard_mode=pb.SHARD_TILES)[0] for k in range(3)]
+    assert np.array_equal(sum(tiles), a) and np.all(sum((t[..., 3] > 0).astype(int) for t in tiles) == 1)
+    parts = [sums([20], rank=k, world=3, shard_mode=pb.SHARD_SAMPLES)[0] for k in range(3)]
+    tot = sum(parts)
+    assert np.array_equal(tot[..., 3], a[..., 3]) and np.allclose(tot[..., :3], a[..., :3], rtol=2e-6, atol=1e-6)
+    # tonemap: monotone in the mean, saturating (colour.rs:62-74)
+    r = pb.Renderer(sc.camera, sc, precision=32, seed=21)
+    r.render_samples(4)
+    img, rgb = r.render().pixels, r.render_rgb24()
+    r.shutdown()
+    m = img[..., 0].ravel()
+    order = np.argsort(m, kind="stable")
+    assert np.all(np.diff(rgb[..., 0].ravel()[order].astype(int)) >= 0)
+    assert np.all(rgb[img >= 1.0] == 255) and np.all(rgb[img <= 0.0] == 0)
