@@ -445,66 +445,6 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend_refill(DevScene
     }
 }
 
-// Speculative variant: a lane that reaches a leaf parks it and keeps descending from its stack, so that the leaf phase of a
-// round runs with as many lanes as possible (ncu on k_extend_refill: triangle tests ran with 6 of 32 lanes).
-template <int ROUNDS, int MIN_REFILL, int KI>
-__global__ void __launch_bounds__(128) k_extend_spec(DevScene sc, PathState<float4> ps, const uint32_t *queue, const uint32_t *count_ptr,
-                                                     uint32_t *cursor) {
-    const uint32_t count = *count_ptr;
-    const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
-    const float4 *__restrict__ nodes = sc.fast_nodes;
-    const float4 *__restrict__ leaves = sc.fast_leaves;
-    int32_t stack[PATHS_FAST_STACK];
-    TravF tv;
-    tv.node = PATHS_TRAV_DONE;
-    bool has = false, exhausted = false;
-    uint32_t slot = 0;
-    int32_t pend = 0; // parked leaf code (< 0) or 0
-    for (;;) {
-        unsigned idle = __ballot_sync(PATHS_FULL_MASK, !has);
-        int n = __popc(idle);
-        if (!exhausted && n >= MIN_REFILL) {
-            int leader = __ffs(idle) - 1;
-            uint32_t base = 0;
-            if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)n);
-            base = __shfl_sync(PATHS_FULL_MASK, base, leader);
-            if (!has) {
-                uint32_t i = base + __popc(idle & lt);
-                if (i < count) {
-                    slot = queue ? queue[i] : i;
-                    float4 o = ps.ray_o[slot], d = ps.ray_d[slot];
-                    tv.init(o.x, o.y, o.z, d.x, d.y, d.z, __int_as_float(0x7f800000), sc.fast_root);
-                    pend = 0;
-                    has = true;
-                }
-            }
-            exhausted = base + (uint32_t)n >= count;
-        }
-        if (!__any_sync(PATHS_FULL_MASK, has)) break;
-#pragma unroll 1
-        for (int r = 0; r < ROUNDS; r++) {
-            if (has) {
-#pragma unroll 1
-                for (int k = 0; k < KI; k++) {
-                    if (tv.node >= 0) tv.inner(nodes, stack);
-                    if (tv.node < 0 && tv.node != PATHS_TRAV_DONE && pend == 0) {
-                        pend = tv.node;
-                        tv.node = tv.pop(stack);
-                    }
-                }
-                if (pend != 0) {
-                    tv.leaf_test<false>(leaves, pend, 0xFFFFFFFFu);
-                    pend = 0;
-                }
-                if (tv.node == PATHS_TRAV_DONE) {
-                    ps.hit[slot] = make_float4(__uint_as_float(tv.prim), tv.t, tv.bx, tv.by);
-                    has = false;
-                }
-            }
-        }
-    }
-}
-
 template <int ROUNDS, int MIN_REFILL>
 __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_shadow_refill(DevScene sc, PathState<float4> ps, const uint32_t *count_ptr, uint32_t *cursor,
                                                        unsigned long long *totals) {
@@ -573,58 +513,6 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_shadow_refill(DevScene
 }
 
 // ------------------------------------------------------------------ four-wide extend / shadow (lane refill, shared-memory stack)
-template <int ROUNDS, int MIN_REFILL, int KI>
-__global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend4(DevScene sc, PathState<float4> ps, const uint32_t *queue, const uint32_t *count_ptr,
-                                                                  uint32_t *cursor) {
-    extern __shared__ int32_t smem_stack[];
-    int32_t *sstack = smem_stack + threadIdx.x;
-    const uint32_t stride = blockDim.x;
-    const uint32_t count = *count_ptr;
-    const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
-    const float4 *__restrict__ nodes4 = sc.fast4_nodes;
-    const float4 *__restrict__ leaves = sc.fast_leaves;
-    TravF4 tv;
-    tv.node = PATHS_TRAV_DONE;
-    bool has = false, exhausted = false;
-    uint32_t slot = 0;
-    for (;;) {
-        unsigned idle = __ballot_sync(PATHS_FULL_MASK, !has);
-        int n = __popc(idle);
-        if (!exhausted && n >= MIN_REFILL) {
-            int leader = __ffs(idle) - 1;
-            uint32_t base = 0;
-            if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)n);
-            base = __shfl_sync(PATHS_FULL_MASK, base, leader);
-            if (!has) {
-                uint32_t i = base + __popc(idle & lt);
-                if (i < count) {
-                    slot = queue ? queue[i] : i;
-                    float4 o = ps.ray_o[slot], d = ps.ray_d[slot];
-                    tv.init(o.x, o.y, o.z, d.x, d.y, d.z, __int_as_float(0x7f800000), sc.fast4_root);
-                    has = true;
-                }
-            }
-            exhausted = base + (uint32_t)n >= count;
-        }
-        if (!__any_sync(PATHS_FULL_MASK, has)) break;
-#pragma unroll 1
-        for (int r = 0; r < ROUNDS; r++) {
-            if (has) {
-#pragma unroll 1
-                for (int k = 0; k < KI && tv.node >= 0; k++) tv.inner4(nodes4, sstack, stride);
-                if (tv.node < 0 && tv.node != PATHS_TRAV_DONE) {
-                    tv.leaf_test<false>(leaves, tv.node, 0xFFFFFFFFu);
-                    tv.node = tv.pop4(sstack, stride);
-                }
-                if (tv.node == PATHS_TRAV_DONE) {
-                    ps.hit[slot] = make_float4(__uint_as_float(tv.prim), tv.t, tv.bx, tv.by);
-                    has = false;
-                }
-            }
-        }
-    }
-}
-
 template <int ROUNDS, int MIN_REFILL, int KI>
 __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_shadow4(DevScene sc, PathState<float4> ps, const uint32_t *count_ptr, uint32_t *cursor,
                                                                   unsigned long long *totals) {
@@ -755,74 +643,6 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend4s(DevScene sc, 
                 if (pend == 0 && tv.node < 0 && tv.node != PATHS_TRAV_DONE) { // reached while the inner phase was cut short
                     pend = tv.node;
                     tv.node = tv.pop4(sstack, stride);
-                }
-                if (pend != 0) {
-                    tv.leaf_test<false>(leaves, pend, 0xFFFFFFFFu);
-                    pend = 0;
-                }
-                if (tv.node == PATHS_TRAV_DONE) {
-                    ps.hit[slot] = make_float4(__uint_as_float(tv.prim), tv.t, tv.bx, tv.by);
-                    has = false;
-                }
-            }
-        }
-    }
-}
-
-// Two-wide counterpart (local-memory stack), same round structure.
-template <int ROUNDS, int MIN_REFILL, int KI, int MIN_INNER>
-__global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend2s(DevScene sc, PathState<float4> ps, const uint32_t *queue, const uint32_t *count_ptr,
-                                                                   uint32_t *cursor) {
-    const uint32_t count = *count_ptr;
-    const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
-    const float4 *__restrict__ nodes = sc.fast_nodes;
-    const float4 *__restrict__ leaves = sc.fast_leaves;
-    int32_t stack[PATHS_FAST_STACK];
-    TravF tv;
-    tv.node = PATHS_TRAV_DONE;
-    bool has = false, exhausted = false;
-    uint32_t slot = 0;
-    int32_t pend = 0;
-    for (;;) {
-        unsigned idle = __ballot_sync(PATHS_FULL_MASK, !has);
-        int n = __popc(idle);
-        if (!exhausted && n >= MIN_REFILL) {
-            int leader = __ffs(idle) - 1;
-            uint32_t base = 0;
-            if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)n);
-            base = __shfl_sync(PATHS_FULL_MASK, base, leader);
-            if (!has) {
-                uint32_t i = base + __popc(idle & lt);
-                if (i < count) {
-                    slot = queue ? queue[i] : i;
-                    float4 o = ps.ray_o[slot], d = ps.ray_d[slot];
-                    tv.init(o.x, o.y, o.z, d.x, d.y, d.z, __int_as_float(0x7f800000), sc.fast_root);
-                    pend = 0;
-                    has = true;
-                }
-            }
-            exhausted = base + (uint32_t)n >= count;
-        }
-        if (!__any_sync(PATHS_FULL_MASK, has)) break;
-#pragma unroll 1
-        for (int r = 0; r < ROUNDS; r++) {
-            const int n_has = __popc(__ballot_sync(PATHS_FULL_MASK, has));
-#pragma unroll 1
-            for (int k = 0; k < KI; k++) {
-                bool inner = has && tv.node >= 0;
-                // leave the inner phase when nobody is at an inner node, or when few are and other lanes wait with a leaf
-                int n_inner = __popc(__ballot_sync(PATHS_FULL_MASK, inner));
-                if (n_inner == 0 || (n_inner < MIN_INNER && n_inner < n_has)) break;
-                if (inner) tv.inner(nodes, stack);
-                if (has && pend == 0 && tv.node < 0 && tv.node != PATHS_TRAV_DONE) {
-                    pend = tv.node;
-                    tv.node = tv.pop(stack);
-                }
-            }
-            if (has) {
-                if (pend == 0 && tv.node < 0 && tv.node != PATHS_TRAV_DONE) {
-                    pend = tv.node;
-                    tv.node = tv.pop(stack);
                 }
                 if (pend != 0) {
                     tv.leaf_test<false>(leaves, pend, 0xFFFFFFFFu);

@@ -223,7 +223,10 @@ template <typename R> class RendererImpl : public RendererBase {
         // traversal kernel: two-wide nodes + local stack for small (L1-resident) scenes, four-wide nodes + shared-memory stack
         // above 64k primitives (measured: teapot 7.5 vs 7.8 ms, dragon 25.4 vs 24.4 ms per 16 spp; profiles/r01_*)
         variant_ = sd_->view.n_prims > 65536u ? 16 : 3;
-        if (const char *v = getenv("PATHS_EXTEND_VARIANT")) variant_ = atoi(v); // development switch between traversal kernels
+        if (const char *v = getenv("PATHS_EXTEND_VARIANT")) { // development switch: 0 plain batches, 3 two-wide refill, 16 four-wide
+            int want = atoi(v);
+            if (want == 0 || want == 3 || want == 16) variant_ = want;
+        }
         if (const char *v = getenv("PATHS_SHADE_VARIANT")) shade_variant_ = atoi(v);
         // ---- persistent grids: every SM full
         int bps = 0;
@@ -237,17 +240,11 @@ template <typename R> class RendererImpl : public RendererBase {
             // four-wide kernels: stack of 3 * depth + 1 levels per thread in shared memory
             smem4_ = (size_t)(3 * sd_->view.fast4_depth + 1) * 128 * sizeof(int32_t);
             if (smem4_ > 200 * 1024) {
-                if (variant_ >= 10 && variant_ < 20) variant_ = 3; // pathological tree: the two-wide kernels keep their stack in local memory
+                if (variant_ == 16) variant_ = 3; // pathological tree: the two-wide kernels keep their stack in local memory
             } else {
-                PATHS_CU(cudaFuncSetAttribute(k_extend4<4, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
-                PATHS_CU(cudaFuncSetAttribute(k_extend4<4, 16, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
-                PATHS_CU(cudaFuncSetAttribute(k_extend4<2, 16, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
                 PATHS_CU(cudaFuncSetAttribute(k_shadow4<4, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
-                PATHS_CU(cudaFuncSetAttribute(k_extend4s<2, 16, 8, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
-                PATHS_CU(cudaFuncSetAttribute(k_extend4s<2, 16, 16, 12>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
-                PATHS_CU(cudaFuncSetAttribute(k_extend4s<4, 16, 8, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
                 PATHS_CU(cudaFuncSetAttribute(k_extend4s<1, 8, 16, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
-                PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_extend4<4, 16, 2>, 128, smem4_));
+                PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_extend4s<1, 8, 16, 8>, 128, smem4_));
                 grid4_ = sm_count_ * std::max(bps, 1);
             }
         }
@@ -258,27 +255,9 @@ template <typename R> class RendererImpl : public RendererBase {
         if constexpr (!IsF64<R>::value) {
             const uint32_t *cnt = pc_.qcount + b;
             uint32_t *cur = pc_.work + 3 * b;
-            switch (variant_) {
-            case 1: k_extend_refill<4, 8><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 2: k_extend_refill<8, 8><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            switch (variant_) { // 0 = one batch of 32 rays per warp at a time (k_extend), kept as the plain baseline
             case 3: k_extend_refill<4, 16><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 4: k_extend_refill<2, 4><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 5: k_extend_refill<1, 1><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 6: k_extend_spec<4, 16, 3><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 7: k_extend_spec<4, 16, 4><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 8: k_extend_spec<2, 16, 6><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 9: k_extend_spec<4, 8, 2><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 10: k_extend4<4, 16, 2><<<grid4_, 128, smem4_, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 11: k_extend4<4, 16, 1><<<grid4_, 128, smem4_, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 12: k_extend4<2, 16, 3><<<grid4_, 128, smem4_, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 13: k_extend4s<2, 16, 8, 8><<<grid4_, 128, smem4_, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 14: k_extend4s<2, 16, 16, 12><<<grid4_, 128, smem4_, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 15: k_extend4s<4, 16, 8, 16><<<grid4_, 128, smem4_, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
             case 16: k_extend4s<1, 8, 16, 8><<<grid4_, 128, smem4_, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 20: k_extend2s<2, 16, 8, 8><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 21: k_extend2s<2, 16, 16, 12><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 22: k_extend2s<4, 16, 8, 16><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 23: k_extend2s<1, 8, 16, 8><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
             default: break;
             }
         }
@@ -287,7 +266,7 @@ template <typename R> class RendererImpl : public RendererBase {
     }
     void launch_shadow(uint32_t b) {
         if constexpr (!IsF64<R>::value) {
-            if (variant_ >= 10 && variant_ < 20) {
+            if (variant_ == 16) {
                 k_shadow4<4, 16, 2><<<grid4_, 128, smem4_, cs_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
                 return;
             }

@@ -1,5 +1,6 @@
 #!/bin/bash
-# development probe: extend-kernel variants on two scenes.  usage: variants.sh "<scenes>" v1 v2 ...   (env PATHS_SHADE_VARIANT passes through)
+# development probe: extend-kernel variants (0 plain batches, 3 two-wide refill, 16 four-wide speculative) on some scenes.
+# usage: variants.sh "<scenes>" v1 v2 ...   (env PATHS_SHADE_VARIANT / PATHS_PIPELINE pass through)
 scenes=$1; shift
 for v in "$@"; do
   for s in $scenes; do
