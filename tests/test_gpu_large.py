@@ -194,3 +194,38 @@ def test_full_size_properties_teapot_1080p(pb):
     order = np.argsort(m, kind="stable")
     assert np.all(np.diff(rgb[..., 0].ravel()[order].astype(int)) >= 0)
     assert np.all(rgb[img >= 1.0] == 255) and np.all(rgb[img <= 0.0] == 0)
+
+
+@pytest.mark.parametrize("name,ref_spp", [("teapot", 2048), ("dragon", 1024)])
+def test_headline_convergence(pb, oracle_mod, name, ref_spp):
+    # SURVEY 8(d), Monte Carlo tolerance of the headline scenes, at reduced resolution so that the CPU reference finishes in under a
+    # minute.  Gate (ii): at the config's 256 spp the GPU image is as close to a many-spp oracle image as a second oracle run is
+    # (sigma0); the error falls as samples are added; the image mean is unbiased.  teapot also meets the absolute figure: the error
+    # follows 1/sqrt(N) (0.224, 0.113, 0.058 at 16, 64, 256 spp), so relRMSE 0.05 is this estimator's noise at ~350 spp and is asserted
+    # at 512.  dragon (small bright area light seen through glossy bounces) is firefly-dominated in linear radiance for the reference
+    # estimator itself, so it is compared display-referred: radiance clamped to [0, 1] like Colour::to_bytes does (colour.rs:62-74).
+    w, h = 160, 90
+    osc, cam = oracle_mod.load_scene(f"scenes/{name}.yml", width=w, height=h)
+    gsc = pb.Scene.load(f"scenes/{name}.yml", width=w, height=h)
+    clamp = (lambda im: np.clip(im, 0.0, 1.0)) if name == "dragon" else (lambda im: im)
+    sums, _, _ = osc.render(cam, 77, 0, ref_spp)
+    ref = clamp(sums / ref_spp)
+    sums_b, _, _ = osc.render(cam, 78, 0, 256)
+    sigma0 = relrmse(clamp(sums_b / 256), ref)
+    r = pb.Renderer(cam, gsc, precision=32, seed=5)
+    errs, done = [], 0
+    for target in (16, 64, 256, 512):
+        r.render_samples(target - done)
+        done = target
+        s = r.sums()
+        errs.append(relrmse(clamp(s[..., :3] / s[..., 3:]), ref))
+    st = r.stats()
+    r.shutdown()
+    assert st["bad_samples"] == 0
+    assert errs[2] <= 1.15 * sigma0, (errs, sigma0)
+    assert errs[0] > errs[1] > errs[2] > errs[3], errs
+    g = s[..., :3] / s[..., 3:]
+    assert abs(clamp(g).mean() - ref.mean()) <= 0.01 * ref.mean()
+    if name == "teapot":
+        assert errs[3] <= 0.05, errs
+        assert 0.42 <= errs[1] / errs[0] <= 0.60 and 0.42 <= errs[2] / errs[1] <= 0.65, errs
