@@ -532,6 +532,12 @@ bool build_device_tree(SceneDevice *sd, const HostScene &hs, DeviceTreeInfo &inf
     BD_CU(cudaMemcpy(nodes4, nodes4_tmp, (size_t)n4 * 128, cudaMemcpyDeviceToDevice));
     int32_t root2 = 0, root4 = 0;
     uint32_t depth2 = h.depth2, depth4 = h.levels4;
+    if (depth2 + n_giants > 60) { // the two-wide kernels keep a 64-entry stack (PATHS_FAST_STACK): a morton tree this deep (long runs
+        cudaEventDestroy(e0);     // of equal keys) goes back to the host SAH builder, whose median fallback keeps trees shallow
+        cudaEventDestroy(e1);
+        err = "small";
+        return false;
+    }
     // ---- giants: a chain above the morton tree's root, largest first is not needed -- every ray tests them all anyway
     if (n_giants > 0) {
         std::vector<HBox> gb(n_giants);

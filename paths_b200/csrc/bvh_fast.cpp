@@ -11,6 +11,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <limits>
+#include <string>
 #include <thread>
 
 #include "host_scene.h"
@@ -340,6 +341,10 @@ bool build_fast_tree(const HostScene &s, FastTree &out, std::string &err) {
     for (size_t i = 0; i < refs.size(); i++) out.leaf_prims[i] = refs[i].prim;
     out.nodes.reserve(refs.size());
     out.depth = emit2(sn, root, out, out.root);
+    if (out.depth > 60) { // PATHS_FAST_STACK is 64 entries
+        err = "production tree deeper than the traversal stack (" + std::to_string(out.depth) + " levels)";
+        return false;
+    }
     for (int a = 0; a < 3; a++) {
         out.root_box[a] = sn[root].box.lo[a];
         out.root_box[3 + a] = sn[root].box.hi[a];
