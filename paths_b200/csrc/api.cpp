@@ -90,7 +90,7 @@ paths_status ensure_staged(paths_scene *s, int device, bool need_ref, bool need_
     }
     if (need_fast && s->device_build) {
         // the GPU builder works on the prim tables in HBM: stage without a production tree, then build in place
-        SceneDevice *sd = upload_scene(device, s->hs, s->has_ref ? &s->ref : nullptr, nullptr, err);
+        SceneDevice *sd = upload_scene(device, s->hs, s->has_ref ? &s->ref : nullptr, nullptr, err, true);
         if (!sd) return fail(PATHS_ERR_CUDA, err);
         DeviceTreeInfo info;
         if (build_device_tree(sd, s->hs, info, err)) {

@@ -87,7 +87,7 @@ template <typename R> __device__ __forceinline__ V3<R> to_world(V3<R> v, V3<R> n
 }
 
 // matrix.rs:94-104, m row-major (stored as double, converted on use)
-template <typename R> __device__ __forceinline__ V3<R> mat_apply(const double *m, V3<R> o) {
+template <typename R, typename S> __device__ __forceinline__ V3<R> mat_apply(const S *m, V3<R> o) {
     return mk3<R>(R(m[0]) * o.x + R(m[1]) * o.y + R(m[2]) * o.z, R(m[3]) * o.x + R(m[4]) * o.y + R(m[5]) * o.z,
                   R(m[6]) * o.x + R(m[7]) * o.y + R(m[8]) * o.z);
 }

@@ -11,18 +11,22 @@ namespace paths {
 #define PATHS_PM_LIGHT 2u
 #define PATHS_LIGHT_ENV 0xFFFFFFFEu /* shadow-record light id of an environment NEE sample */
 
-struct DevObject {          // src/scene.rs:35-40 + src/geom.rs:98-122 + resolved material record
+// S = storage type of the real-valued fields: double for the parity / mixed instantiations, float for the production f32 kernels
+// (the same values rounded once on the host instead of once per shaded hit: no 8-byte loads, no f64 -> f32 conversions in k_shade)
+template <typename S> struct DevObjectT { // src/scene.rs:35-40 + src/geom.rs:98-122 + resolved material record
     int32_t shape, smooth;
     uint32_t vert_base, face_base;
-    double rot[9];
+    S rot[9];
     int32_t mat_type, vertex_albedo;
-    double albedo[3];
-    double r0, metalness, roughness;
+    S albedo[3];
+    S r0, metalness, roughness;
     // Fresnel combination, brdf() only
     int32_t d_type, s_type;
-    double d_albedo[3], s_albedo[3];
-    double d_r0, d_metal, d_rough, s_r0, s_metal, s_rough, fresnel_r0;
+    S d_albedo[3], s_albedo[3];
+    S d_r0, d_metal, d_rough, s_r0, s_metal, s_rough, fresnel_r0;
 };
+typedef DevObjectT<double> DevObject;
+typedef DevObjectT<float> DevObjectF;
 
 struct DevLight { // src/scene.rs:42-66
     int32_t geometry;
@@ -63,6 +67,11 @@ struct DevScene {
     const double *vertex_normals; // 3 per vertex, concatenated over models
     const double *vertex_colours; // 3 per vertex
     const uint32_t *faces;        // 3 per face
+    // ---- f32 mirrors read by the production shade kernel (null unless the production tree is staged)
+    const float4 *prim_shade;     // 2 per prim: {flags, entity, face, -} as bits | triangle: rotated face normal, sphere: centre
+    const DevObjectF *objects32;
+    const float4 *vertex_normals32; // xyz per vertex
+    const float4 *vertex_colours32;
     int32_t sky_type;
     double sky_c0[3], sky_c1[3];
     uint32_t sky_w, sky_h;

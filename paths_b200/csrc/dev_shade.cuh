@@ -110,7 +110,7 @@ template <typename R> struct Material {
     MatR<R> diffuse, specular;
 };
 
-template <typename R> __device__ __forceinline__ Material<R> load_material(const DevObject &o) {
+template <typename R, typename S> __device__ __forceinline__ Material<R> load_material(const DevObjectT<S> &o) {
     Material<R> mt;
     mt.m.type = o.mat_type;
     mt.m.albedo = mk3<R>(R(o.albedo[0]), R(o.albedo[1]), R(o.albedo[2]));

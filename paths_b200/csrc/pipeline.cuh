@@ -100,6 +100,42 @@ __global__ void __launch_bounds__(128) k_extend(DevScene sc, PathState<typename 
     }
 }
 
+// ------------------------------------------------------------------ which copy of the shading tables an instantiation reads
+template <typename R> struct ShadeTables { // f64 (parity and mixed modes): the reference-precision tables
+    typedef DevObject Object;
+    static __device__ __forceinline__ void prim(const DevScene &sc, uint32_t prim, uint4 &meta, V3<R> &gvec) {
+        meta = sc.prim_meta[prim];
+        const double *g = sc.prim_geom + (size_t)prim * 12;
+        gvec = (meta.x & PATHS_PM_TRI) ? mk3<R>(R(g[9]), R(g[10]), R(g[11])) : mk3<R>(R(g[0]), R(g[1]), R(g[2]));
+    }
+    static __device__ __forceinline__ const DevObject *objects(const DevScene &sc) { return sc.objects; }
+    static __device__ __forceinline__ V3<R> vertex_normal(const DevScene &sc, size_t v) {
+        const double *p = sc.vertex_normals + 3 * v;
+        return mk3<R>(R(p[0]), R(p[1]), R(p[2]));
+    }
+    static __device__ __forceinline__ V3<R> vertex_colour(const DevScene &sc, size_t v) {
+        const double *p = sc.vertex_colours + 3 * v;
+        return mk3<R>(R(p[0]), R(p[1]), R(p[2]));
+    }
+};
+template <> struct ShadeTables<float> { // production: f32 mirrors
+    typedef DevObjectF Object;
+    static __device__ __forceinline__ void prim(const DevScene &sc, uint32_t prim, uint4 &meta, V3<float> &gvec) {
+        const float4 a = __ldg(sc.prim_shade + 2 * (size_t)prim), b = __ldg(sc.prim_shade + 2 * (size_t)prim + 1);
+        meta = make_uint4(__float_as_uint(a.x), __float_as_uint(a.y), __float_as_uint(a.z), 0u);
+        gvec = mk3<float>(b.x, b.y, b.z);
+    }
+    static __device__ __forceinline__ const DevObjectF *objects(const DevScene &sc) { return sc.objects32; }
+    static __device__ __forceinline__ V3<float> vertex_normal(const DevScene &sc, size_t v) {
+        const float4 n = __ldg(sc.vertex_normals32 + v);
+        return mk3<float>(n.x, n.y, n.z);
+    }
+    static __device__ __forceinline__ V3<float> vertex_colour(const DevScene &sc, size_t v) {
+        const float4 c = __ldg(sc.vertex_colours32 + v);
+        return mk3<float>(c.x, c.y, c.z);
+    }
+};
+
 // ------------------------------------------------------------------ shade: one iteration of trace_ray's loop body (src/trace.rs:13-118)
 template <typename R> struct ShadeOut {
     bool alive, shadow, shadow2; // shadow2: environment NEE sample (extension)
@@ -135,30 +171,32 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
         return;
     }
     // ---- Collision (geom.rs:59-70) + Scene::find_intersection post-processing (scene.rs:172-197)
-    const uint4 meta = sc.prim_meta[prim];
-    const double *g = sc.prim_geom + (size_t)prim * 12;
+    // The production instantiation reads f32 mirrors of the tables (the same values, rounded once on the host): one 32-byte record
+    // per primitive instead of a 16-byte and a 96-byte one, float4 vertex normals, a float object record.
+    typedef typename ShadeTables<R>::Object ObjectT;
+    uint4 meta;
+    V3<R> gvec; // triangle: rotated face normal; sphere: centre
+    ShadeTables<R>::prim(sc, prim, meta, gvec);
     R t = h4.y, bx = h4.z, by = h4.w;
     V3<R> location = ro + (rd * t);
     V3<R> normal;
     bool is_tri = (meta.x & PATHS_PM_TRI) != 0;
     if (is_tri) { // geom.rs:293-302
-        V3<R> n = mk3<R>(R(g[9]), R(g[10]), R(g[11]));
-        R cos_theta = dot(n, rd);
-        normal = cos_theta > R(0) ? neg(n) : n;
+        R cos_theta = dot(gvec, rd);
+        normal = cos_theta > R(0) ? neg(gvec) : gvec;
     } else { // geom.rs:228-234
-        normal = normed(location - mk3<R>(R(g[0]), R(g[1]), R(g[2])));
+        normal = normed(location - gvec);
     }
     bool is_light = (meta.x & PATHS_PM_LIGHT) != 0;
     R bz = R(1.0) - bx - by;
-    const DevObject *obj = is_light ? nullptr : sc.objects + meta.y;
+    const ObjectT *obj = is_light ? nullptr : ShadeTables<R>::objects(sc) + meta.y;
     const uint32_t *face = nullptr;
     if (obj && obj->shape == 1 && is_tri) {
         face = sc.faces + 3 * ((size_t)obj->face_base + meta.z);
         if (obj->smooth) { // model.rs:142-156 (un-normalised, not flipped) then Mesh::rotate (geom.rs:119-121)
-            const double *vn = sc.vertex_normals + 3 * (size_t)obj->vert_base;
-            V3<R> an = mk3<R>(R(vn[3 * face[0]]), R(vn[3 * face[0] + 1]), R(vn[3 * face[0] + 2]));
-            V3<R> bn = mk3<R>(R(vn[3 * face[1]]), R(vn[3 * face[1] + 1]), R(vn[3 * face[1] + 2]));
-            V3<R> cn = mk3<R>(R(vn[3 * face[2]]), R(vn[3 * face[2] + 1]), R(vn[3 * face[2] + 2]));
+            V3<R> an = ShadeTables<R>::vertex_normal(sc, obj->vert_base + face[0]);
+            V3<R> bn = ShadeTables<R>::vertex_normal(sc, obj->vert_base + face[1]);
+            V3<R> cn = ShadeTables<R>::vertex_normal(sc, obj->vert_base + face[2]);
             V3<R> sn = an * bx + bn * by + cn * bz;
             normal = mat_apply<R>(obj->rot, sn);
         }
@@ -181,10 +219,9 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
     mat.m.ggx = mat.diffuse.ggx = mat.specular.ggx = (ext & PATHS_EXT_GGX) != 0;
     const bool micro = (ext & (PATHS_EXT_MICROFACET | PATHS_EXT_MICROFACET_COSINE)) != 0 && (mat.fresnel || mat.m.type == 3);
     if (face && !mat.fresnel && (mat.m.type == 0 || mat.m.type == 2) && obj->vertex_albedo) {
-        const double *vc = sc.vertex_colours + 3 * (size_t)obj->vert_base;
-        V3<R> ac = mk3<R>(R(vc[3 * face[0]]), R(vc[3 * face[0] + 1]), R(vc[3 * face[0] + 2]));
-        V3<R> bc = mk3<R>(R(vc[3 * face[1]]), R(vc[3 * face[1] + 1]), R(vc[3 * face[1] + 2]));
-        V3<R> cc = mk3<R>(R(vc[3 * face[2]]), R(vc[3 * face[2] + 1]), R(vc[3 * face[2] + 2]));
+        V3<R> ac = ShadeTables<R>::vertex_colour(sc, obj->vert_base + face[0]);
+        V3<R> bc = ShadeTables<R>::vertex_colour(sc, obj->vert_base + face[1]);
+        V3<R> cc = ShadeTables<R>::vertex_colour(sc, obj->vert_base + face[2]);
         mat.m.albedo = ac * bx + bc * by + cc * bz;
     }
     // block 0 = {light choice, light u, light v, gloss choice}; block 1 = {hemisphere u, v, roulette, -}: generated only when read

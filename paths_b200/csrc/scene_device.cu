@@ -50,7 +50,7 @@ DevCamera make_dev_camera(const paths_camera &c) {
     return d;
 }
 
-SceneDevice *upload_scene(int device, const HostScene &hs, const RefTree *ref, const FastTree *fast, std::string &err) {
+SceneDevice *upload_scene(int device, const HostScene &hs, const RefTree *ref, const FastTree *fast, std::string &err, bool want_f32_tables) {
     cudaError_t e = cudaSetDevice(device);
     if (e != cudaSuccess) {
         err = std::string("cudaSetDevice: ") + cudaGetErrorString(e);
@@ -177,6 +177,41 @@ SceneDevice *upload_scene(int device, const HostScene &hs, const RefTree *ref, c
             vn[3 * i] = hs.vertex_normals[i].x;
             vn[3 * i + 1] = hs.vertex_normals[i].y;
             vn[3 * i + 2] = hs.vertex_normals[i].z;
+        }
+        if (fast || want_f32_tables) { // f32 mirrors for the production shade kernel
+            std::vector<DevObjectF> objs32(objs.size());
+            for (size_t i = 0; i < objs.size(); i++) {
+                const DevObject &a = objs[i];
+                DevObjectF &b = objs32[i];
+                std::memset(&b, 0, sizeof(b));
+                b.shape = a.shape; b.smooth = a.smooth; b.vert_base = a.vert_base; b.face_base = a.face_base;
+                for (int k = 0; k < 9; k++) b.rot[k] = (float)a.rot[k];
+                b.mat_type = a.mat_type; b.vertex_albedo = a.vertex_albedo;
+                for (int k = 0; k < 3; k++) {
+                    b.albedo[k] = (float)a.albedo[k];
+                    b.d_albedo[k] = (float)a.d_albedo[k];
+                    b.s_albedo[k] = (float)a.s_albedo[k];
+                }
+                b.r0 = (float)a.r0; b.metalness = (float)a.metalness; b.roughness = (float)a.roughness;
+                b.d_type = a.d_type; b.s_type = a.s_type;
+                b.d_r0 = (float)a.d_r0; b.d_metal = (float)a.d_metal; b.d_rough = (float)a.d_rough;
+                b.s_r0 = (float)a.s_r0; b.s_metal = (float)a.s_metal; b.s_rough = (float)a.s_rough;
+                b.fresnel_r0 = (float)a.fresnel_r0;
+            }
+            std::vector<float4> vn32(hs.vertex_normals.size()), vc32(hs.vertex_colours.size() / 3), ps32(hs.prims.size() * 2);
+            for (size_t i = 0; i < vn32.size(); i++)
+                vn32[i] = make_float4((float)hs.vertex_normals[i].x, (float)hs.vertex_normals[i].y, (float)hs.vertex_normals[i].z, 0.0f);
+            for (size_t i = 0; i < vc32.size(); i++)
+                vc32[i] = make_float4((float)hs.vertex_colours[3 * i], (float)hs.vertex_colours[3 * i + 1], (float)hs.vertex_colours[3 * i + 2], 0.0f);
+            for (size_t i = 0; i < hs.prims.size(); i++) {
+                const HostPrim &p = hs.prims[i];
+                uint32_t m[4] = {(p.type == 1 ? PATHS_PM_TRI : 0u) | (p.is_light ? PATHS_PM_LIGHT : 0u), p.entity, p.face, 0u};
+                std::memcpy(&ps32[2 * i], m, 16);
+                const D3 &g = p.type == 1 ? p.n : p.a;
+                ps32[2 * i + 1] = make_float4((float)g.x, (float)g.y, (float)g.z, 0.0f);
+            }
+            ok = ok && put(sd, objs32, &v.objects32, err) && put(sd, vn32, &v.vertex_normals32, err) && put(sd, vc32, &v.vertex_colours32, err) &&
+                 put(sd, ps32, &v.prim_shade, err);
         }
         ok = ok && put(sd, objs, &v.objects, err) && put(sd, lights, &v.lights, err) && put(sd, vn, &v.vertex_normals, err) &&
              put(sd, hs.vertex_colours, &v.vertex_colours, err) && put(sd, hs.faces, &v.faces, err) && put(sd, hs.sky_texels, &v.sky_texels, err) &&

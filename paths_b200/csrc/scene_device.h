@@ -16,8 +16,10 @@ struct SceneDevice {
     ~SceneDevice();
 };
 
-// Uploads the scene; ref / fast may be null (the matching kernels then must not be used).
-SceneDevice *upload_scene(int device, const HostScene &hs, const RefTree *ref, const FastTree *fast, std::string &err);
+// Uploads the scene; ref / fast may be null (the matching kernels then must not be used).  The f32 mirrors of the shading tables
+// go with the production tree (fast != null, or want_f32_tables when that tree is about to be built on the device).
+SceneDevice *upload_scene(int device, const HostScene &hs, const RefTree *ref, const FastTree *fast, std::string &err,
+                          bool want_f32_tables = false);
 
 // ---- production tree built on the device (bvh_device.cu)
 struct DeviceTreeInfo {
