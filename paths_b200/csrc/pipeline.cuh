@@ -20,6 +20,9 @@ namespace paths {
 #ifndef PATHS_LB_SHADE
 #define PATHS_LB_SHADE 5
 #endif
+#ifndef PATHS_LB_SHADE_PLAIN
+#define PATHS_LB_SHADE_PLAIN 6 /* no lights, no extensions: the kernel without next-event estimation fits 6 blocks */
+#endif
 #ifndef PATHS_LB_SHADE64
 #define PATHS_LB_SHADE64 4
 #endif
@@ -143,7 +146,9 @@ template <typename R> struct ShadeOut {
     uint32_t light;
 };
 
-template <typename R>
+// LIGHTS: the scene has lights (next-event estimation is compiled in); EXT: any estimator extension is on.  The common kernels --
+// no extensions, with or without lights -- carry none of the other code and keep their registers for occupancy.
+template <typename R, bool LIGHTS, bool EXT>
 __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typename Vec4T<R>::type> &ps, uint32_t slot, uint32_t pixel, uint32_t S,
                                            uint32_t k0, uint32_t k1, uint32_t max_bounces, uint32_t ext, unsigned long long *totals, ShadeOut<R> &out) {
     typedef typename Vec4T<R>::type R4;
@@ -158,7 +163,7 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
     out.alive = false;
     out.shadow = false;
     out.shadow2 = false;
-    const bool env_nee = (ext & PATHS_EXT_ENV_NEE) && sc.sky_type == 2;
+    const bool env_nee = EXT && (ext & PATHS_EXT_ENV_NEE) && sc.sky_type == 2;
 
     if (prim == 0xFFFFFFFFu) { // trace.rs:20-23
         // with environment NEE the sky is accounted for at the previous vertex unless that bounce was specular (same rule
@@ -216,8 +221,8 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
     }
     // ---- material resolve (trace.rs:44-50, material.rs:39-49,183-195, model.rs:158-172)
     Material<R> mat = load_material<R>(*obj);
-    mat.m.ggx = mat.diffuse.ggx = mat.specular.ggx = (ext & PATHS_EXT_GGX) != 0;
-    const bool micro = (ext & (PATHS_EXT_MICROFACET | PATHS_EXT_MICROFACET_COSINE)) != 0 && (mat.fresnel || mat.m.type == 3);
+    mat.m.ggx = mat.diffuse.ggx = mat.specular.ggx = EXT && (ext & PATHS_EXT_GGX) != 0;
+    const bool micro = EXT && (ext & (PATHS_EXT_MICROFACET | PATHS_EXT_MICROFACET_COSINE)) != 0 && (mat.fresnel || mat.m.type == 3);
     if (face && !mat.fresnel && (mat.m.type == 0 || mat.m.type == 2) && obj->vertex_albedo) {
         V3<R> ac = ShadeTables<R>::vertex_colour(sc, obj->vert_base + face[0]);
         V3<R> bc = ShadeTables<R>::vertex_colour(sc, obj->vert_base + face[1]);
@@ -228,13 +233,13 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
     U4 r0, r1;
     r0.v[0] = r0.v[1] = r0.v[2] = r0.v[3] = 0u;
     r1 = r0;
-    if (sc.n_lights > 0 || mat.m.type == 2 || micro) r0 = philox4x32_10(pixel, S, loops * 2u, PATHS_TAG_PATH, k0, k1);
+    if (LIGHTS || mat.m.type == 2 || micro) r0 = philox4x32_10(pixel, S, loops * 2u, PATHS_TAG_PATH, k0, k1);
     if (loops >= 2 || mat.m.type == 0 || mat.m.type == 2 || micro) r1 = philox4x32_10(pixel, S, loops * 2u + 1u, PATHS_TAG_PATH, k0, k1);
     V3<R> vec_out = neg(rd);
     V3<R> new_origin = location + normal * R(0.0001); // trace.rs:57,89
 
     // ---- next event estimation (trace.rs:53-82)
-    if (sc.n_lights > 0) {
+    if (LIGHTS) {
         uint32_t nl = sc.n_lights;
         uint32_t id = min(nl - 1u, (uint32_t)(u01<R>(r0.v[0]) * R(nl))); // scene.rs:199-206
         const DevLight &light = sc.lights[id];
@@ -247,7 +252,7 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
             V3<R> base = mk3<R>(R(light.colour[0]), R(light.colour[1]), R(light.colour[2])) * R(light.intensity);
             V3<R> brdf = material_brdf<R>(mat, vec_out, neg(sdir), normal);
             V3<R> direct = base * brdf * inv_pdf;
-            if (ext & PATHS_EXT_NEE_ALL_LIGHTS) direct = direct * R(nl); // extension: undo the uniform light choice
+            if (EXT && (ext & PATHS_EXT_NEE_ALL_LIGHTS)) direct = direct * R(nl); // extension: undo the uniform light choice
             if (col_bad(direct)) atomicAdd(totals + 2, 1ull); // Colour::check (trace.rs:80)
             V3<R> contrib = direct * throughput;
             // a zero contribution cannot change the estimate: skip its visibility query
@@ -308,8 +313,8 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
     (void)black;
 }
 
-template <typename R>
-__global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : PATHS_LB_SHADE)) k_shade(DevScene sc, PathState<typename Vec4T<R>::type> ps, ShardInfo shard, uint32_t s_base, uint32_t k0,
+template <typename R, bool LIGHTS, bool EXT>
+__global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LIGHTS || EXT) ? PATHS_LB_SHADE : PATHS_LB_SHADE_PLAIN)) k_shade(DevScene sc, PathState<typename Vec4T<R>::type> ps, ShardInfo shard, uint32_t s_base, uint32_t k0,
                                                uint32_t k1, uint32_t max_bounces, uint32_t ext, const uint32_t *queue, uint32_t *queue_next,
                                                const uint32_t *count_ptr, uint32_t *next_count, uint32_t *shadow_count, uint32_t *cursor,
                                                unsigned long long *totals) {
@@ -344,15 +349,15 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : PAT
             uint32_t lp, k;
             shard.split(slot, lp, k);
             uint32_t pixel = shard.pixels ? shard.pixels[lp] : lp;
-            shade_path<R>(sc, ps, slot, pixel, s_base + k, k0, k1, max_bounces, ext, totals, out);
+            shade_path<R, LIGHTS, EXT>(sc, ps, slot, pixel, s_base + k, k0, k1, max_bounces, ext, totals, out);
         }
-        uint32_t spos = warp_append(shadow_count, out.shadow);
-        if (out.shadow) {
+        uint32_t spos = LIGHTS ? warp_append(shadow_count, out.shadow) : 0u;
+        if (LIGHTS && out.shadow) {
             ps.sh_o[spos] = mk4(out.sh_o.x, out.sh_o.y, out.sh_o.z, bits_to_real(out.light, R(0)));
             ps.sh_d[spos] = mk4(out.sh_d.x, out.sh_d.y, out.sh_d.z, bits_to_real(slot, R(0)));
             ps.sh_c[spos] = mk4(out.sh_c.x, out.sh_c.y, out.sh_c.z, R(0));
         }
-        if (ext & PATHS_EXT_ENV_NEE) { // warp-uniform
+        if (EXT && (ext & PATHS_EXT_ENV_NEE)) { // warp-uniform
             uint32_t epos = warp_append(shadow_count, out.shadow2);
             if (out.shadow2) {
                 ps.sh_o[epos] = mk4(out.sh_o.x, out.sh_o.y, out.sh_o.z, bits_to_real(PATHS_LIGHT_ENV, R(0)));

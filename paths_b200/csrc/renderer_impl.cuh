@@ -233,7 +233,12 @@ template <typename R> class RendererImpl : public RendererBase {
         if constexpr (IsF64<R>::value) PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (k_extend<R, false>), 128, 0));
         else PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_extend_refill<4, 16>, 128, 0));
         grid_trace_ = sm_count_ * std::max(bps, 1);
-        PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_shade<R>, 128, 0));
+        {
+            const bool lights = sd_->view.n_lights > 0, ext = opts_.extensions != 0;
+            if (ext) PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (k_shade<R, true, true>), 128, 0));
+            else if (lights) PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (k_shade<R, true, false>), 128, 0));
+            else PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (k_shade<R, false, false>), 128, 0));
+        }
         grid_shade_ = sm_count_ * std::max(bps, 1);
         grid_stream_ = sm_count_ * 8;
         if constexpr (!IsF64<R>::value) {
@@ -302,9 +307,18 @@ template <typename R> class RendererImpl : public RendererBase {
             toc();
             stats_.n_extend_launches++;
             tic(2);
-            k_shade<R><<<grid_shade_, 128, 0, cs_>>>(sd_->view, ps_, shard, s_base, k0, k1, opts_.max_bounces, opts_.extensions, q,
-                                                        pc_.queue[(b + 1) & 1],
-                                                        pc_.qcount + b, pc_.qcount + b + 1, pc_.scount + b, shade_variant_ == 1 ? nullptr : pc_.work + 3 * b + 1, pc_.totals);
+            {
+                uint32_t *shade_cursor = shade_variant_ == 1 ? nullptr : pc_.work + 3 * b + 1;
+                uint32_t *qn = pc_.queue[(b + 1) & 1];
+                // three instantiations: every extension compiled in (lights or not) / lights only / neither
+#define PATHS_SHADE_ARGS sd_->view, ps_, shard, s_base, k0, k1, opts_.max_bounces, opts_.extensions, q, qn, pc_.qcount + b, pc_.qcount + b + 1, pc_.scount + b, shade_cursor, pc_.totals
+                if (opts_.extensions != 0) {
+                    if (sd_->view.n_lights > 0) k_shade<R, true, true><<<grid_shade_, 128, 0, cs_>>>(PATHS_SHADE_ARGS);
+                    else k_shade<R, false, true><<<grid_shade_, 128, 0, cs_>>>(PATHS_SHADE_ARGS);
+                } else if (sd_->view.n_lights > 0) k_shade<R, true, false><<<grid_shade_, 128, 0, cs_>>>(PATHS_SHADE_ARGS);
+                else k_shade<R, false, false><<<grid_shade_, 128, 0, cs_>>>(PATHS_SHADE_ARGS);
+#undef PATHS_SHADE_ARGS
+            }
             toc();
             if (sd_->view.n_lights > 0 || ((opts_.extensions & PATHS_EXT_ENV_NEE) && sd_->view.sky_type == 2)) {
                 tic(3);

@@ -79,7 +79,11 @@ def test_device_tree_dragon(pb, oracle_mod):
     assert gsc.check_bvh() == 0
     info = gsc.info
     assert info["bvh_builder"] == 1 and info["giant_prims"] == 6
-    assert info["build_ms_device"] < 200.0  # the host SAH build takes about a second
+    # build time: the first build of a process also pays for loading the builder's kernels, so a second staging is timed
+    gsc.build_bvh()
+    gsc.build_bvh(device=True)
+    assert gsc.check_bvh() == 0
+    assert gsc.info["build_ms_device"] < 100.0  # the host SAH build takes 0.5 - 0.9 s
     o, d, _ = oracle_mod.camera_rays(cam, 4, 0)
     o32, d32 = o.astype(np.float32).astype(np.float64), d.astype(np.float32).astype(np.float64)
     r0, u0, b0 = osc.trace_closest(o32, d32, want_bary=True)
