@@ -103,6 +103,37 @@ __global__ void __launch_bounds__(128) k_extend(DevScene sc, PathState<typename 
     }
 }
 
+// ------------------------------------------------------------------ camera segment of the production path: raygen + closest hit
+// Primary rays of neighbouring slots are nearly parallel, so a warp's 32 rays walk the tree together: plain batches of 32
+// (no lane refill) are the faster schedule here (-2..3.5 % extend time), and generating the ray in the same kernel hides
+// raygen's 128 B/slot of HBM writes behind the traversal and saves reading the ray back (64 B/slot).
+template <typename R> // float only; a template so that both translation units may include this header
+__global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_camera_extend(DevScene sc, DevCamera cam, uint32_t k0, uint32_t k1, ShardInfo shard,
+                                                                        uint32_t s_base, uint32_t n_slots, PathState<float4> ps, PassControl pc,
+                                                                        uint32_t *cursor) {
+    const uint32_t lane = threadIdx.x & 31u;
+    if (blockIdx.x == 0 && threadIdx.x == 0) pc.qcount[0] = n_slots;
+    for (;;) {
+        uint32_t base = warp_fetch(cursor);
+        if (base >= n_slots) break;
+        uint32_t i = base + lane;
+        if (i < n_slots) {
+            uint32_t lp, k;
+            shard.split(i, lp, k);
+            uint32_t pixel = shard.pixels ? shard.pixels[lp] : lp;
+            V3<float> o, d;
+            float w;
+            pixel_sample_ray<float>(cam, k0, k1, pixel, s_base + k, o, d, w);
+            ps.ray_o[i] = make_float4(o.x, o.y, o.z, 0.0f);
+            ps.ray_d[i] = make_float4(d.x, d.y, d.z, 0.0f);
+            ps.thr[i] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(PATHS_FLAG_SPECULAR)); // trace.rs:8-11
+            ps.col[i] = make_float4(0.0f, 0.0f, 0.0f, w);
+            HitF h = trace_fast<false>(sc, o.x, o.y, o.z, d.x, d.y, d.z, __int_as_float(0x7f800000), 0xFFFFFFFFu);
+            ps.hit[i] = make_float4(__uint_as_float(h.prim), h.t, h.bx, h.by);
+        }
+    }
+}
+
 // ------------------------------------------------------------------ which copy of the shading tables an instantiation reads
 template <typename R> struct ShadeTables { // f64 (parity and mixed modes): the reference-precision tables
     typedef DevObject Object;

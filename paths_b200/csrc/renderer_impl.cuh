@@ -40,6 +40,8 @@ template <typename R> class RendererImpl : public RendererBase {
     uint32_t samples_done_ = 0; // global samples per pixel issued so far (all ranks together)
     int sm_count_ = 148, grid_trace_ = 0, grid_shade_ = 0, grid_stream_ = 0, variant_ = 3, grid4_ = 0, shade_variant_ = 1;
     size_t smem4_ = 0;
+    int variant_b0_ = 1; // camera segment: 1 = raygen fused with a plain-batch closest hit, 0/3/16 = k_raygen + that extend variant
+    int grid_camera_ = 0;
     // device buffers
     R4 *sums_ = nullptr;
     uint32_t *pixels_ = nullptr; // tile shard: local -> global pixel
@@ -228,11 +230,16 @@ template <typename R> class RendererImpl : public RendererBase {
             if (want == 0 || want == 3 || want == 16) variant_ = want;
         }
         if (const char *v = getenv("PATHS_SHADE_VARIANT")) shade_variant_ = atoi(v);
+        if (const char *v = getenv("PATHS_EXTEND_B0")) variant_b0_ = atoi(v);
         // ---- persistent grids: every SM full
         int bps = 0;
         if constexpr (IsF64<R>::value) PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (k_extend<R, false>), 128, 0));
         else PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_extend_refill<4, 16>, 128, 0));
         grid_trace_ = sm_count_ * std::max(bps, 1);
+        if constexpr (!IsF64<R>::value) {
+            PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_camera_extend<float>, 128, 0));
+            grid_camera_ = sm_count_ * std::max(bps, 1);
+        }
         {
             const bool lights = sd_->view.n_lights > 0, ext = opts_.extensions != 0;
             if (ext) PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (k_shade<R, true, true>), 128, 0));
@@ -260,7 +267,8 @@ template <typename R> class RendererImpl : public RendererBase {
         if constexpr (!IsF64<R>::value) {
             const uint32_t *cnt = pc_.qcount + b;
             uint32_t *cur = pc_.work + 3 * b;
-            switch (variant_) { // 0 = one batch of 32 rays per warp at a time (k_extend), kept as the plain baseline
+            int vsel = (b == 0 && variant_b0_ >= 0) ? variant_b0_ : variant_;
+            switch (vsel) { // 0 = one batch of 32 rays per warp at a time (k_extend), kept as the plain baseline
             case 3: k_extend_refill<4, 16><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
             case 16: k_extend4s<1, 8, 16, 8><<<grid4_, 128, smem4_, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
             default: break;
@@ -297,13 +305,20 @@ template <typename R> class RendererImpl : public RendererBase {
         shard.n_local_magic = n_local > 1 ? (uint32_t)((1ull << 32) / n_local) : 0xFFFFFFFFu;
         const uint32_t nb = opts_.max_bounces + 1; // segments per path (trace.rs:13-16)
         PATHS_CU(cudaMemsetAsync(ctl_block_, 0, n_ctl_ * sizeof(uint32_t), cs_));
-        tic(0);
-        k_raygen<R><<<grid_stream_, 256, 0, cs_>>>(cam_, k0, k1, shard, s_base, n_slots, ps_, pc_);
-        toc();
+        bool fused_camera = false;
+        if constexpr (!IsF64<R>::value) fused_camera = variant_b0_ == 1;
+        if (!fused_camera) {
+            tic(0);
+            k_raygen<R><<<grid_stream_, 256, 0, cs_>>>(cam_, k0, k1, shard, s_base, n_slots, ps_, pc_);
+            toc();
+        }
         for (uint32_t b = 0; b < nb; b++) {
             const uint32_t *q = b == 0 ? nullptr : pc_.queue[b & 1];
             tic(1);
-            launch_extend(q, b);
+            if (b == 0 && fused_camera) {
+                if constexpr (!IsF64<R>::value)
+                    k_camera_extend<float><<<grid_camera_, 128, 0, cs_>>>(sd_->view, cam_, k0, k1, shard, s_base, n_slots, ps_, pc_, pc_.work);
+            } else launch_extend(q, b);
             toc();
             stats_.n_extend_launches++;
             tic(2);
