@@ -36,6 +36,18 @@ template <> struct IsF64<double> {
 };
 
 template <typename R> __device__ __forceinline__ typename Vec4T<R>::type ld4(const typename Vec4T<R>::type *p) { return *p; }
+// Path records are read once and written once per kernel: streaming (evict-first) accesses keep them from pushing the scene
+// tables out of L1/L2.
+__device__ __forceinline__ float4 ld_rec(const float4 *p) { return __ldcs(p); }
+__device__ __forceinline__ double4 ld_rec(const double4 *p) {
+    double2 a = __ldcs(reinterpret_cast<const double2 *>(p)), b = __ldcs(reinterpret_cast<const double2 *>(p) + 1);
+    return make_double4(a.x, a.y, b.x, b.y);
+}
+__device__ __forceinline__ void st_rec(float4 *p, float4 v) { __stcs(p, v); }
+__device__ __forceinline__ void st_rec(double4 *p, double4 v) {
+    __stcs(reinterpret_cast<double2 *>(p), make_double2(v.x, v.y));
+    __stcs(reinterpret_cast<double2 *>(p) + 1, make_double2(v.z, v.w));
+}
 
 __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
@@ -68,10 +80,10 @@ __global__ void __launch_bounds__(256) k_raygen(DevCamera cam, uint32_t k0, uint
         V3<R> o, d;
         R w;
         pixel_sample_ray<R>(cam, k0, k1, pixel, s_base + k, o, d, w);
-        ps.ray_o[i] = mk4(o.x, o.y, o.z, R(0));
-        ps.ray_d[i] = mk4(d.x, d.y, d.z, R(0));
-        ps.thr[i] = mk4(R(1), R(1), R(1), bits_to_real(PATHS_FLAG_SPECULAR, R(0))); // trace.rs:8-11
-        ps.col[i] = mk4(R(0), R(0), R(0), w);
+        st_rec(&ps.ray_o[i], mk4(o.x, o.y, o.z, R(0)));
+        st_rec(&ps.ray_d[i], mk4(d.x, d.y, d.z, R(0)));
+        st_rec(&ps.thr[i], mk4(R(1), R(1), R(1), bits_to_real(PATHS_FLAG_SPECULAR, R(0)))); // trace.rs:8-11
+        st_rec(&ps.col[i], mk4(R(0), R(0), R(0), w));
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) pc.qcount[0] = n_slots;
 }
@@ -88,16 +100,16 @@ __global__ void __launch_bounds__(128) k_extend(DevScene sc, PathState<typename 
         uint32_t i = base + lane;
         if (i < count) {
             uint32_t slot = queue ? queue[i] : i;
-            typename Vec4T<R>::type o = ps.ray_o[slot], d = ps.ray_d[slot];
+            typename Vec4T<R>::type o = ld_rec(&ps.ray_o[slot]), d = ld_rec(&ps.ray_d[slot]);
             if constexpr (IsF64<R>::value) {
                 Hit64 h = MIXED ? trace_mixed<false>(sc, mk3((double)o.x, (double)o.y, (double)o.z), mk3((double)d.x, (double)d.y, (double)d.z),
                                                      (double)__int_as_float(0x7f800000), 0xFFFFFFFFu)
                                 : trace_ref(sc, mk3((double)o.x, (double)o.y, (double)o.z), mk3((double)d.x, (double)d.y, (double)d.z));
-                ps.hit[slot] = mk4(bits_to_real(h.prim, R(0)), R(h.t), R(h.bx), R(h.by));
+                st_rec(&ps.hit[slot], mk4(bits_to_real(h.prim, R(0)), R(h.t), R(h.bx), R(h.by)));
             } else {
                 HitF h = trace_fast<false>(sc, (float)o.x, (float)o.y, (float)o.z, (float)d.x, (float)d.y, (float)d.z, __int_as_float(0x7f800000),
                                            0xFFFFFFFFu);
-                ps.hit[slot] = mk4(bits_to_real(h.prim, R(0)), R(h.t), R(h.bx), R(h.by));
+                st_rec(&ps.hit[slot], mk4(bits_to_real(h.prim, R(0)), R(h.t), R(h.bx), R(h.by)));
             }
         }
     }
@@ -124,12 +136,12 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_camera_extend(DevScene
             V3<float> o, d;
             float w;
             pixel_sample_ray<float>(cam, k0, k1, pixel, s_base + k, o, d, w);
-            ps.ray_o[i] = make_float4(o.x, o.y, o.z, 0.0f);
-            ps.ray_d[i] = make_float4(d.x, d.y, d.z, 0.0f);
-            ps.thr[i] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(PATHS_FLAG_SPECULAR)); // trace.rs:8-11
-            ps.col[i] = make_float4(0.0f, 0.0f, 0.0f, w);
+            st_rec(&ps.ray_o[i], make_float4(o.x, o.y, o.z, 0.0f));
+            st_rec(&ps.ray_d[i], make_float4(d.x, d.y, d.z, 0.0f));
+            st_rec(&ps.thr[i], make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(PATHS_FLAG_SPECULAR))); // trace.rs:8-11
+            st_rec(&ps.col[i], make_float4(0.0f, 0.0f, 0.0f, w));
             HitF h = trace_fast<false>(sc, o.x, o.y, o.z, d.x, d.y, d.z, __int_as_float(0x7f800000), 0xFFFFFFFFu);
-            ps.hit[i] = make_float4(__uint_as_float(h.prim), h.t, h.bx, h.by);
+            st_rec(&ps.hit[i], make_float4(__uint_as_float(h.prim), h.t, h.bx, h.by));
         }
     }
 }
@@ -413,7 +425,7 @@ __global__ void __launch_bounds__(128) k_shadow(DevScene sc, PathState<typename 
         if (base >= count) break;
         uint32_t i = base + lane;
         if (i < count) {
-            R4 o = ps.sh_o[i], d = ps.sh_d[i];
+            R4 o = ld_rec(&ps.sh_o[i]), d = ld_rec(&ps.sh_d[i]);
             uint32_t lid = real_to_bits(o.w), slot = real_to_bits(d.w);
             bool occluded;
             if constexpr (IsF64<R>::value && MIXED) {
@@ -455,13 +467,13 @@ __global__ void __launch_bounds__(128) k_shadow(DevScene sc, PathState<typename 
                 occluded = h.prim != 0xFFFFFFFFu;
             }
             if (!occluded) { // trace.rs:81: colour += direct * throughput
-                R4 c = ps.sh_c[i];
-                R4 col = ps.col[slot];
+                R4 c = ld_rec(&ps.sh_c[i]);
+                R4 col = ld_rec(&ps.col[slot]);
                 col.x += c.x;
                 col.y += c.y;
                 col.z += c.z;
                 if (col.x < R(0) || col.y < R(0) || col.z < R(0)) atomicAdd(totals + 2, 1ull); // Colour::check (trace.rs:82)
-                ps.col[slot] = col;
+                st_rec(&ps.col[slot], col);
             }
         }
     }
@@ -495,7 +507,7 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend_refill(DevScene
                 uint32_t i = base + __popc(idle & lt);
                 if (i < count) {
                     slot = queue ? queue[i] : i;
-                    float4 o = ps.ray_o[slot], d = ps.ray_d[slot];
+                    float4 o = ld_rec(&ps.ray_o[slot]), d = ld_rec(&ps.ray_d[slot]);
                     tv.init(o.x, o.y, o.z, d.x, d.y, d.z, __int_as_float(0x7f800000), sc.fast_root);
                     has = true;
                 }
@@ -510,7 +522,7 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend_refill(DevScene
                 for (int k = 0; k < 3 && tv.node >= 0; k++) tv.inner(nodes, stack);
                 if (tv.node < 0 && tv.node != PATHS_TRAV_DONE) tv.leaf<false>(leaves, stack, 0xFFFFFFFFu);
                 if (tv.node == PATHS_TRAV_DONE) {
-                    ps.hit[slot] = make_float4(__uint_as_float(tv.prim), tv.t, tv.bx, tv.by);
+                    st_rec(&ps.hit[slot], make_float4(__uint_as_float(tv.prim), tv.t, tv.bx, tv.by));
                     has = false;
                 }
             }
@@ -542,7 +554,7 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_shadow_refill(DevScene
                 uint32_t i = base + __popc(idle & lt);
                 if (i < count) {
                     rec = i;
-                    float4 o = ps.sh_o[i], d = ps.sh_d[i];
+                    float4 o = ld_rec(&ps.sh_o[i]), d = ld_rec(&ps.sh_d[i]);
                     uint32_t lid = __float_as_uint(o.w);
                     slot = __float_as_uint(d.w);
                     float t_light = __int_as_float(0x7f800000);
@@ -573,11 +585,11 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_shadow_refill(DevScene
                 if (tv.node < 0 && tv.node != PATHS_TRAV_DONE) occluded = tv.leaf<true>(leaves, stack, skip);
                 if (occluded) has = false;
                 else if (tv.node == PATHS_TRAV_DONE) {
-                    float4 c = ps.sh_c[rec];
-                    float4 col = ps.col[slot];
+                    float4 c = ld_rec(&ps.sh_c[rec]);
+                    float4 col = ld_rec(&ps.col[slot]);
                     col.x += c.x; col.y += c.y; col.z += c.z;
                     if (col.x < 0.0f || col.y < 0.0f || col.z < 0.0f) atomicAdd(totals + 2, 1ull);
-                    ps.col[slot] = col;
+                    st_rec(&ps.col[slot], col);
                     has = false;
                 }
             }
@@ -612,7 +624,7 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_shadow4(DevScene sc, P
                 uint32_t i = base + __popc(idle & lt);
                 if (i < count) {
                     rec = i;
-                    float4 o = ps.sh_o[i], d = ps.sh_d[i];
+                    float4 o = ld_rec(&ps.sh_o[i]), d = ld_rec(&ps.sh_d[i]);
                     uint32_t lid = __float_as_uint(o.w);
                     slot = __float_as_uint(d.w);
                     float t_light = __int_as_float(0x7f800000);
@@ -646,11 +658,11 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_shadow4(DevScene sc, P
                 }
                 if (occluded) has = false;
                 else if (tv.node == PATHS_TRAV_DONE) {
-                    float4 c = ps.sh_c[rec];
-                    float4 col = ps.col[slot];
+                    float4 c = ld_rec(&ps.sh_c[rec]);
+                    float4 col = ld_rec(&ps.col[slot]);
                     col.x += c.x; col.y += c.y; col.z += c.z;
                     if (col.x < 0.0f || col.y < 0.0f || col.z < 0.0f) atomicAdd(totals + 2, 1ull);
-                    ps.col[slot] = col;
+                    st_rec(&ps.col[slot], col);
                     has = false;
                 }
             }
@@ -688,7 +700,7 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend4s(DevScene sc, 
                 uint32_t i = base + __popc(idle & lt);
                 if (i < count) {
                     slot = queue ? queue[i] : i;
-                    float4 o = ps.ray_o[slot], d = ps.ray_d[slot];
+                    float4 o = ld_rec(&ps.ray_o[slot]), d = ld_rec(&ps.ray_d[slot]);
                     tv.init(o.x, o.y, o.z, d.x, d.y, d.z, __int_as_float(0x7f800000), sc.fast4_root);
                     pend = 0;
                     has = true;
@@ -722,7 +734,7 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend4s(DevScene sc, 
                     pend = 0;
                 }
                 if (tv.node == PATHS_TRAV_DONE) {
-                    ps.hit[slot] = make_float4(__uint_as_float(tv.prim), tv.t, tv.bx, tv.by);
+                    st_rec(&ps.hit[slot], make_float4(__uint_as_float(tv.prim), tv.t, tv.bx, tv.by));
                     has = false;
                 }
             }
@@ -740,7 +752,7 @@ __global__ void __launch_bounds__(256) k_accumulate(PathState<typename Vec4T<R>:
         uint32_t pixel = shard.pixels ? shard.pixels[lp] : lp;
         R4 s = sums[pixel];
         for (uint32_t k = 0; k < spp_pass; k++) {
-            R4 c = ps.col[(size_t)k * shard.n_local + lp];
+            R4 c = ld_rec(&ps.col[(size_t)k * shard.n_local + lp]);
             s.x += c.x * c.w;
             s.y += c.y * c.w;
             s.z += c.z * c.w;
