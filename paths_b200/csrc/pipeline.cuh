@@ -17,6 +17,9 @@ namespace paths {
 #ifndef PATHS_LB_EXTEND
 #define PATHS_LB_EXTEND 8
 #endif
+#ifndef PATHS_QBUF
+#define PATHS_QBUF 160u /* per-warp staging of next-queue entries in the shade kernel */
+#endif
 #ifndef PATHS_LB_SHADE
 #define PATHS_LB_SHADE 5
 #endif
@@ -365,6 +368,14 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LI
     const uint32_t lane = threadIdx.x & 31u;
     // cursor == nullptr: batches of 32 entries are dealt to the warps of the grid round-robin (shading cost per entry is
     // uniform enough) -- no fetch atomic on the critical path; the next batch's records are prefetched into L2 meanwhile
+    __shared__ uint32_t qbuf_all[4][PATHS_QBUF];
+    uint32_t *qbuf = qbuf_all[threadIdx.x >> 5];
+    uint32_t fill = 0; // warp-uniform
+    typedef typename Vec4T<R>::type R4;
+    constexpr uint32_t SBUF = LIGHTS ? (IsF64<R>::value ? 64u : 96u) : 1u; // shadow records staged per warp (origin | direction | contribution)
+    __shared__ R4 sbuf_all[4][3 * SBUF];
+    R4 *sbuf = sbuf_all[threadIdx.x >> 5];
+    uint32_t sfill = 0; // warp-uniform
     const uint32_t warp_stride = gridDim.x * (blockDim.x >> 5) * 32u;
     uint32_t static_base = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 32u;
     for (;;) {
@@ -394,11 +405,28 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LI
             uint32_t pixel = shard.pixels ? shard.pixels[lp] : lp;
             shade_path<R, LIGHTS, EXT>(sc, ps, slot, pixel, s_base + k, k0, k1, max_bounces, ext, totals, out);
         }
-        uint32_t spos = LIGHTS ? warp_append(shadow_count, out.shadow) : 0u;
-        if (LIGHTS && out.shadow) {
-            ps.sh_o[spos] = mk4(out.sh_o.x, out.sh_o.y, out.sh_o.z, bits_to_real(out.light, R(0)));
-            ps.sh_d[spos] = mk4(out.sh_d.x, out.sh_d.y, out.sh_d.z, bits_to_real(slot, R(0)));
-            ps.sh_c[spos] = mk4(out.sh_c.x, out.sh_c.y, out.sh_c.z, R(0));
+        if (LIGHTS) { // shadow records: staged per warp like the queue entries below, appended SBUF - 32 or more at a time
+            const unsigned m = __ballot_sync(PATHS_FULL_MASK, out.shadow);
+            if (out.shadow) {
+                const uint32_t k = sfill + __popc(m & ((1u << lane) - 1u));
+                sbuf[k] = mk4(out.sh_o.x, out.sh_o.y, out.sh_o.z, bits_to_real(out.light, R(0)));
+                sbuf[SBUF + k] = mk4(out.sh_d.x, out.sh_d.y, out.sh_d.z, bits_to_real(slot, R(0)));
+                sbuf[2 * SBUF + k] = mk4(out.sh_c.x, out.sh_c.y, out.sh_c.z, R(0));
+            }
+            sfill += __popc(m);
+            if (sfill > SBUF - 32u) {
+                __syncwarp();
+                uint32_t sbase = 0;
+                if (lane == 0) sbase = atomicAdd(shadow_count, sfill);
+                sbase = __shfl_sync(PATHS_FULL_MASK, sbase, 0);
+                for (uint32_t k = lane; k < sfill; k += 32u) {
+                    ps.sh_o[sbase + k] = sbuf[k];
+                    ps.sh_d[sbase + k] = sbuf[SBUF + k];
+                    ps.sh_c[sbase + k] = sbuf[2 * SBUF + k];
+                }
+                sfill = 0;
+                __syncwarp();
+            }
         }
         if (EXT && (ext & PATHS_EXT_ENV_NEE)) { // warp-uniform
             uint32_t epos = warp_append(shadow_count, out.shadow2);
@@ -408,8 +436,40 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LI
                 ps.sh_c[epos] = mk4(out.sh2_c.x, out.sh2_c.y, out.sh2_c.z, R(0));
             }
         }
-        uint32_t qpos = warp_append(next_count, out.alive);
-        if (out.alive) queue_next[qpos] = slot;
+        // surviving paths: gathered per warp in shared memory and appended to the next queue PATHS_QBUF - 32 or more at a time
+        // (one counter atomic and a few full-line stores per flush instead of one atomic per batch)
+        {
+            const unsigned m = __ballot_sync(PATHS_FULL_MASK, out.alive);
+            if (out.alive) qbuf[fill + __popc(m & ((1u << lane) - 1u))] = slot;
+            fill += __popc(m);
+            if (fill > PATHS_QBUF - 32u) {
+                __syncwarp();
+                uint32_t qbase = 0;
+                if (lane == 0) qbase = atomicAdd(next_count, fill);
+                qbase = __shfl_sync(PATHS_FULL_MASK, qbase, 0);
+                for (uint32_t k = lane; k < fill; k += 32u) queue_next[qbase + k] = qbuf[k];
+                fill = 0;
+                __syncwarp();
+            }
+        }
+    }
+    if (LIGHTS && sfill > 0) {
+        __syncwarp();
+        uint32_t sbase = 0;
+        if (lane == 0) sbase = atomicAdd(shadow_count, sfill);
+        sbase = __shfl_sync(PATHS_FULL_MASK, sbase, 0);
+        for (uint32_t k = lane; k < sfill; k += 32u) {
+            ps.sh_o[sbase + k] = sbuf[k];
+            ps.sh_d[sbase + k] = sbuf[SBUF + k];
+            ps.sh_c[sbase + k] = sbuf[2 * SBUF + k];
+        }
+    }
+    if (fill > 0) {
+        __syncwarp();
+        uint32_t qbase = 0;
+        if (lane == 0) qbase = atomicAdd(next_count, fill);
+        qbase = __shfl_sync(PATHS_FULL_MASK, qbase, 0);
+        for (uint32_t k = lane; k < fill; k += 32u) queue_next[qbase + k] = qbuf[k];
     }
 }
 
