@@ -541,7 +541,7 @@ __global__ void __launch_bounds__(128) k_shadow(DevScene sc, PathState<typename 
 // Persistent warps; a lane whose ray has ended takes the next queue entry as soon as MIN_REFILL lanes of its warp are idle,
 // instead of waiting for the slowest ray of a batch of 32.  ROUNDS bounded traversal rounds run between two refill checks;
 // one round = up to three inner nodes, then at most one leaf.
-template <int ROUNDS, int MIN_REFILL>
+template <int ROUNDS, int MIN_REFILL, int KI = 3>
 __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend_refill(DevScene sc, PathState<float4> ps, const uint32_t *queue, const uint32_t *count_ptr,
                                                        uint32_t *cursor) {
     const uint32_t count = *count_ptr;
@@ -577,7 +577,7 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend_refill(DevScene
         for (int r = 0; r < ROUNDS; r++) {
             if (has) {
 #pragma unroll 1
-                for (int k = 0; k < 3 && tv.node >= 0; k++) tv.inner(nodes, stack);
+                for (int k = 0; k < KI && tv.node >= 0; k++) tv.inner(nodes, stack);
                 if (tv.node < 0 && tv.node != PATHS_TRAV_DONE) tv.leaf<false>(leaves, stack, 0xFFFFFFFFu);
                 if (tv.node == PATHS_TRAV_DONE) {
                     st_rec(&ps.hit[2 * slot], make_float4(__uint_as_float(tv.prim), tv.t, tv.bx, tv.by));
@@ -588,7 +588,7 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend_refill(DevScene
     }
 }
 
-template <int ROUNDS, int MIN_REFILL>
+template <int ROUNDS, int MIN_REFILL, int KI = 3>
 __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_shadow_refill(DevScene sc, PathState<float4> ps, const uint32_t *count_ptr, uint32_t *cursor,
                                                        unsigned long long *totals) {
     const uint32_t count = *count_ptr;
@@ -638,7 +638,7 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_shadow_refill(DevScene
         for (int r = 0; r < ROUNDS; r++) {
             if (has) {
 #pragma unroll 1
-                for (int k = 0; k < 3 && tv.node >= 0; k++) tv.inner(nodes, stack);
+                for (int k = 0; k < KI && tv.node >= 0; k++) tv.inner(nodes, stack);
                 bool occluded = false;
                 if (tv.node < 0 && tv.node != PATHS_TRAV_DONE) occluded = tv.leaf<true>(leaves, stack, skip);
                 if (occluded) has = false;

@@ -237,7 +237,7 @@ template <typename R> class RendererImpl : public RendererBase {
         // ---- persistent grids: every SM full
         int bps = 0;
         if constexpr (IsF64<R>::value) PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (k_extend<R, false>), 128, 0));
-        else PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_extend_refill<4, 16>, 128, 0));
+        else PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (k_extend_refill<1, 16, 8>), 128, 0));
         grid_trace_ = sm_count_ * std::max(bps, 1);
         if constexpr (!IsF64<R>::value) {
             PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_camera_extend<float>, 128, 0));
@@ -258,8 +258,8 @@ template <typename R> class RendererImpl : public RendererBase {
                 if (variant_ == 16) variant_ = 3; // pathological tree: the two-wide kernels keep their stack in local memory
             } else {
                 PATHS_CU(cudaFuncSetAttribute(k_shadow4<4, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
-                PATHS_CU(cudaFuncSetAttribute(k_extend4s<1, 8, 16, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
-                PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_extend4s<1, 8, 16, 8>, 128, smem4_));
+                PATHS_CU(cudaFuncSetAttribute(k_extend4s<1, 16, 16, 12>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
+                PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_extend4s<1, 16, 16, 12>, 128, smem4_));
                 grid4_ = sm_count_ * std::max(bps, 1);
             }
         }
@@ -272,8 +272,8 @@ template <typename R> class RendererImpl : public RendererBase {
             uint32_t *cur = pc_.work + 3 * b;
             int vsel = (b == 0 && variant_b0_ >= 0) ? variant_b0_ : variant_;
             switch (vsel) { // 0 = one batch of 32 rays per warp at a time (k_extend), kept as the plain baseline
-            case 3: k_extend_refill<4, 16><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 16: k_extend4s<1, 8, 16, 8><<<grid4_, 128, smem4_, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 3: k_extend_refill<1, 16, 8><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 16: k_extend4s<1, 16, 16, 12><<<grid4_, 128, smem4_, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
             default: break;
             }
         }
@@ -282,12 +282,12 @@ template <typename R> class RendererImpl : public RendererBase {
     }
     void launch_shadow(uint32_t b) {
         if constexpr (!IsF64<R>::value) {
-            if (variant_ == 16) {
+if (variant_ == 16) {
                 k_shadow4<4, 16, 2><<<grid4_, 128, smem4_, cs_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
                 return;
             }
             if (variant_ != 0) {
-                k_shadow_refill<4, 8><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
+                k_shadow_refill<1, 16, 8><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
                 return;
             }
         }
