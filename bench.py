@@ -330,7 +330,7 @@ def run_ours(args, rank, world, local_rank):
                                    + " sharding, NCCL reduce of the float4 buffer per step"
                        if world > 1 else f"{yaml} at {W}x{H}, {S} spp per step", "scene": args.scene, "width": W, "height": H,
                        "spp_per_step_per_gpu": S, "prims": info["n_prims"], "seed": args.seed,
-                       "l2": "per-pass path state (8.3M slots x 136 B = 1.1 GB) streams through HBM and exceeds the 126 MB L2; the scene tables "
+                       "l2": "per-pass path state (33M slots x 136 B = 4.5 GB per pass context) streams through HBM and exceeds the 126 MB L2; the scene tables "
                              "(BVH + triangles, ~1 MB) are L2-resident by design"},
             "mrays_per_sec": (tot_ext + tot_shadow) / (ms * 1e-3) / 1e6,
             "rays_per_sample": (tot_ext + tot_shadow) / max(tot_samples, 1),
@@ -340,7 +340,7 @@ def run_ours(args, rank, world, local_rank):
                             + (", NCCL reduce of the float4 buffers to rank 0 inside the timed region" if world > 1 else "")},
             "gpu_launches": int(tot_launch),
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic, "traffic_source": traffic_src,
-                         "kernel": "k_extend<float>", "launches": int(n_ext_launch), "avg_launch_ms": ext_ms / n_ext_launch,
+                         "kernel": "closest-hit kernels: k_camera_extend (raygen + camera segment) and k_extend_refill<1,16,8> (bounces)", "launches": int(n_ext_launch), "avg_launch_ms": ext_ms / n_ext_launch,
                          "algorithmic_bytes_per_ray": Q, "algorithmic_bytes_per_sample": per_sample,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst)" if peaks else "fallback 6650",
                          "kernel_share_of_step": ext_ms / max(dt_["ms_total"], 1e-9),
