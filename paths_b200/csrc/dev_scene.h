@@ -90,9 +90,10 @@ struct DevCamera { // src/camera.rs:12-27 after CameraDescription::to_camera (sr
 // One wavefront pass keeps n_slots camera paths in flight.  Slot i carries sample (s_base + i / n_local) of local pixel
 // (i % n_local).  Path state stays in its slot for the whole pass; queues hold slot indices.
 template <typename R4> struct PathState {
-    // Two interleaved pairs, one 32-byte sector each: {origin, direction} at ray_o[2 * slot], ray_d[2 * slot] (ray_d = ray_o + 1) and
-    // {hit, throughput} at hit[2 * slot], thr[2 * slot] (thr = hit + 1).  Bounce queues are sparse in slot order, and a 16-byte record
-    // of its own would drag its dead neighbour's half of the sector through DRAM (ncu: 2.1 x the useful bytes on bounce 1).
+    // {origin, direction} are an interleaved pair, one 32-byte sector: ray_o[2 * slot], ray_d[2 * slot] with ray_d = ray_o + 1.  Bounce
+    // queues are sparse in slot order, and a 16-byte record of its own drags its dead neighbour's half of the sector through DRAM
+    // (ncu: 2.1 x the useful bytes on bounce 1).  hit and thr stay separate arrays: paired, the 16-byte hit write of the extend kernels
+    // became a partial-sector write that L2 completes by reading the sector first (+100 B/ray of DRAM traffic for the same run time).
     R4 *ray_o; // origin xyz
     R4 *ray_d; // direction xyz
     R4 *hit;   // prim bits, t, bx, by

@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(256) k_raygen(DevCamera cam, uint32_t k0, uint
         pixel_sample_ray<R>(cam, k0, k1, pixel, s_base + k, o, d, w);
         st_rec(&ps.ray_o[2 * i], mk4(o.x, o.y, o.z, R(0)));
         st_rec(&ps.ray_d[2 * i], mk4(d.x, d.y, d.z, R(0)));
-        st_rec(&ps.thr[2 * i], mk4(R(1), R(1), R(1), bits_to_real(PATHS_FLAG_SPECULAR, R(0)))); // trace.rs:8-11
+        st_rec(&ps.thr[i], mk4(R(1), R(1), R(1), bits_to_real(PATHS_FLAG_SPECULAR, R(0)))); // trace.rs:8-11
         st_rec(&ps.col[i], mk4(R(0), R(0), R(0), w));
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) pc.qcount[0] = n_slots;
@@ -108,11 +108,11 @@ __global__ void __launch_bounds__(128) k_extend(DevScene sc, PathState<typename 
                 Hit64 h = MIXED ? trace_mixed<false>(sc, mk3((double)o.x, (double)o.y, (double)o.z), mk3((double)d.x, (double)d.y, (double)d.z),
                                                      (double)__int_as_float(0x7f800000), 0xFFFFFFFFu)
                                 : trace_ref(sc, mk3((double)o.x, (double)o.y, (double)o.z), mk3((double)d.x, (double)d.y, (double)d.z));
-                st_rec(&ps.hit[2 * slot], mk4(bits_to_real(h.prim, R(0)), R(h.t), R(h.bx), R(h.by)));
+                st_rec(&ps.hit[slot], mk4(bits_to_real(h.prim, R(0)), R(h.t), R(h.bx), R(h.by)));
             } else {
                 HitF h = trace_fast<false>(sc, (float)o.x, (float)o.y, (float)o.z, (float)d.x, (float)d.y, (float)d.z, __int_as_float(0x7f800000),
                                            0xFFFFFFFFu);
-                st_rec(&ps.hit[2 * slot], mk4(bits_to_real(h.prim, R(0)), R(h.t), R(h.bx), R(h.by)));
+                st_rec(&ps.hit[slot], mk4(bits_to_real(h.prim, R(0)), R(h.t), R(h.bx), R(h.by)));
             }
         }
     }
@@ -141,10 +141,10 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_camera_extend(DevScene
             pixel_sample_ray<float>(cam, k0, k1, pixel, s_base + k, o, d, w);
             st_rec(&ps.ray_o[2 * i], make_float4(o.x, o.y, o.z, 0.0f));
             st_rec(&ps.ray_d[2 * i], make_float4(d.x, d.y, d.z, 0.0f));
-            st_rec(&ps.thr[2 * i], make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(PATHS_FLAG_SPECULAR))); // trace.rs:8-11
+            st_rec(&ps.thr[i], make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(PATHS_FLAG_SPECULAR))); // trace.rs:8-11
             st_rec(&ps.col[i], make_float4(0.0f, 0.0f, 0.0f, w));
             HitF h = trace_fast<false>(sc, o.x, o.y, o.z, d.x, d.y, d.z, __int_as_float(0x7f800000), 0xFFFFFFFFu);
-            st_rec(&ps.hit[2 * i], make_float4(__uint_as_float(h.prim), h.t, h.bx, h.by));
+            st_rec(&ps.hit[i], make_float4(__uint_as_float(h.prim), h.t, h.bx, h.by));
         }
     }
 }
@@ -199,7 +199,7 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
                                            uint32_t k0, uint32_t k1, uint32_t max_bounces, uint32_t ext, unsigned long long *totals, ShadeOut<R> &out) {
     typedef typename Vec4T<R>::type R4;
     const V3<R> black = mk3<R>(R(0), R(0), R(0));
-    R4 o4 = ps.ray_o[2 * slot], d4 = ps.ray_d[2 * slot], h4 = ps.hit[2 * slot], t4 = ps.thr[2 * slot];
+    R4 o4 = ps.ray_o[2 * slot], d4 = ps.ray_d[2 * slot], h4 = ps.hit[slot], t4 = ps.thr[slot];
     V3<R> ro = mk3<R>(o4.x, o4.y, o4.z), rd = mk3<R>(d4.x, d4.y, d4.z);
     V3<R> throughput = mk3<R>(t4.x, t4.y, t4.z);
     uint32_t flags = real_to_bits(t4.w);
@@ -354,7 +354,7 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
     if (loops > max_bounces) return; // trace.rs:14-16
     ps.ray_o[2 * slot] = mk4(new_origin.x, new_origin.y, new_origin.z, R(0));
     ps.ray_d[2 * slot] = mk4(direction.x, direction.y, direction.z, R(0));
-    ps.thr[2 * slot] = mk4(throughput.x, throughput.y, throughput.z, bits_to_real(loops | (is_specular ? PATHS_FLAG_SPECULAR : 0u), R(0)));
+    ps.thr[slot] = mk4(throughput.x, throughput.y, throughput.z, bits_to_real(loops | (is_specular ? PATHS_FLAG_SPECULAR : 0u), R(0)));
     out.alive = true;
     (void)black;
 }
@@ -388,7 +388,7 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LI
             if (in < count && base < count) {
                 uint32_t sn = queue ? __ldg(queue + in) : in;
                 prefetch_l2(ps.ray_o + 2 * sn); // {origin, direction}
-                prefetch_l2(ps.hit + 2 * sn);   // {hit, throughput}
+                prefetch_l2(ps.hit + sn); prefetch_l2(ps.thr + sn);
             }
         }
         if (base >= count) break;
@@ -580,7 +580,7 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend_refill(DevScene
                 for (int k = 0; k < KI && tv.node >= 0; k++) tv.inner(nodes, stack);
                 if (tv.node < 0 && tv.node != PATHS_TRAV_DONE) tv.leaf<false>(leaves, stack, 0xFFFFFFFFu);
                 if (tv.node == PATHS_TRAV_DONE) {
-                    st_rec(&ps.hit[2 * slot], make_float4(__uint_as_float(tv.prim), tv.t, tv.bx, tv.by));
+                    st_rec(&ps.hit[slot], make_float4(__uint_as_float(tv.prim), tv.t, tv.bx, tv.by));
                     has = false;
                 }
             }
@@ -792,7 +792,7 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend4s(DevScene sc, 
                     pend = 0;
                 }
                 if (tv.node == PATHS_TRAV_DONE) {
-                    st_rec(&ps.hit[2 * slot], make_float4(__uint_as_float(tv.prim), tv.t, tv.bx, tv.by));
+                    st_rec(&ps.hit[slot], make_float4(__uint_as_float(tv.prim), tv.t, tv.bx, tv.by));
                     has = false;
                 }
             }

@@ -201,12 +201,11 @@ template <typename R> class RendererImpl : public RendererBase {
             PassCtx &x = ctx_[c];
             std::memset(&x.ps, 0, sizeof(x.ps));
             std::memset(&x.pc, 0, sizeof(x.pc));
-            // {origin, direction} and {hit, throughput} are interleaved pairs (dev_scene.h)
-            if (alloc(&x.ps.ray_o, 2 * n_slots_max_) != PATHS_OK || alloc(&x.ps.hit, 2 * n_slots_max_) != PATHS_OK ||
-                alloc(&x.ps.col, n_slots_max_) != PATHS_OK)
+            // {origin, direction} is an interleaved pair (dev_scene.h)
+            if (alloc(&x.ps.ray_o, 2 * n_slots_max_) != PATHS_OK || alloc(&x.ps.hit, n_slots_max_) != PATHS_OK ||
+                alloc(&x.ps.thr, n_slots_max_) != PATHS_OK || alloc(&x.ps.col, n_slots_max_) != PATHS_OK)
                 return PATHS_ERR_CUDA;
             x.ps.ray_d = x.ps.ray_o + 1;
-            x.ps.thr = x.ps.hit + 1;
             // shadow records: one per path and bounce for light NEE, one more with environment NEE
             size_t n_shadow = n_slots_max_ * ((opts_.extensions & PATHS_EXT_ENV_NEE) ? 2 : 1);
             R4 **shadow[] = {&x.ps.sh_o, &x.ps.sh_d, &x.ps.sh_c};
