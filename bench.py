@@ -44,6 +44,15 @@ def ensure_assets(scene):
         import make_assets
 
         make_assets.ensure(*ASSETS[scene])
+
+
+def also_scenes(args):
+    """BASELINE.json quotes the metric on teapot AND dragon: the default (teapot) run of our arm adds a short dragon leg."""
+    if args.impl != "ours" or args.scene != "teapot" or args.also in ("", "none"):
+        return []
+    return [x for x in args.also.split(",") if x in SCENES and x != args.scene]
+
+
 METRIC = "path_samples_per_sec"
 UNIT = "samples/s"
 
@@ -301,6 +310,29 @@ def run_ours(args, rank, world, local_rank):
     e2e_value = e2e_steps * S * world * W * H / e2e_dt
     re_.shutdown()
 
+    # ---- BASELINE's second scene (dragon): a short device-timed leg of the same step, outside the headline's timed region
+    others = {}
+    for name in also_scenes(args):
+        yaml2, W2, H2 = SCENES[name]
+        scene2 = pb.Scene.load(yaml2, width=W2, height=H2)
+        r2 = pb.Renderer(scene2.camera, scene2, device=local_rank, precision=args.precision, seed=args.seed, rank=rank, world=world,
+                         shard_mode=pb.SHARD_TILES if args.shard == "tiles" else pb.SHARD_SAMPLES, time_kernels=False)
+        k2 = max(3, min(args.steps, 5))
+        ms2, d2, _ = timed_region(r2, k2, 3, False)
+        r2.shutdown()
+        tot2 = torch.tensor([d2["samples"], d2["extend_rays"] + d2["shadow_rays"]], device="cuda", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(tot2, op=dist.ReduceOp.SUM)
+        smp2, rays2 = [float(x) for x in tot2.tolist()]
+        others[name] = {"value": smp2 / (ms2 * 1e-3), "unit": UNIT, "mrays_per_sec": rays2 / (ms2 * 1e-3) / 1e6, "ms_per_step": ms2 / k2,
+                        "steps": k2, "warmup": 3, "n_gpus": world, "spp_per_step_per_gpu": S, "prims": scene2.info["n_prims"],
+                        "workload": f"{yaml2} at {W2}x{H2}, {S} spp per GPU per step"
+                                    + (" (asset absent: synthetic 871k-triangle stand-in mesh, tools/make_assets.py)" if name == "dragon" else "")}
+        if rank == 0 and args.cpu_budget > 0:
+            cpu2, _, _, _ = cpu_reference_leg(yaml2, W2, H2, min(args.cpu_budget, 6.0))
+            others[name]["cpu_baseline"] = cpu2
+        del scene2
+
     line = None
     if rank == 0:
         # ---- CPU baseline + algorithmic bytes (the only use of oracle/ in this arm)
@@ -349,6 +381,8 @@ def run_ours(args, rank, world, local_rank):
                                  "the production SAH tree visits fewer nodes and the scene is cache-resident, so frac can exceed 1"},
             "cpu_baseline": cpu,
         }
+        if others:
+            line["other_scenes"] = others
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -368,14 +402,17 @@ def main():
                     help="N > 1: each GPU renders a sample range of every pixel (default) or all samples of its 64x64 tiles")
     ap.add_argument("--precision", type=int, default=0, choices=[0, 32, 64])
     ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--also", default="dragon", help="comma-separated extra scenes timed briefly after the teapot headline (none = skip)")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for the cpu_baseline leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if rank == 0:
-        ensure_assets(args.scene)
+    if rank == 0 or args.impl == "ours":
+        ensure_assets(args.scene)     # every rank: generation is written under a private name and renamed
+        for extra in also_scenes(args):
+            ensure_assets(extra)
     if args.impl == "reference":
         run_reference(args, rank)
         return

@@ -155,7 +155,10 @@ def ensure(*names):
         fn = MAKERS[n]
         default = fn.__defaults__[0]
         if not Path(default).exists():
-            fn()
+            # written under a private name and renamed: several ranks of one bench may get here at the same time
+            tmp = Path(default).with_name(Path(default).name + f".tmp{os.getpid()}")
+            fn(tmp)
+            os.replace(tmp, default)
         out[n] = str(default)
     return out
 
