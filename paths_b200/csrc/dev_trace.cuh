@@ -465,7 +465,9 @@ struct TravF {
 // The stack lives in shared memory as stack[level * blockDim.x + thread] (conflict-free); its depth is sized by the host from
 // the tree (3 * depth + 1 entries always suffice), so there is no overflow path.
 struct TravF4 : TravF {
-    __device__ __forceinline__ void inner4(const float4 *__restrict__ nodes4, int32_t *sstack, uint32_t stride) {
+    // SORT = false (visibility rays): any occluder will do, so the hit children are taken in slot order and the exchange network
+    // (25 of ~110 instructions per node) is left out
+    template <bool SORT = true> __device__ __forceinline__ void inner4(const float4 *__restrict__ nodes4, int32_t *sstack, uint32_t stride) {
         const float4 *n = nodes4 + 8 * (size_t)node;
         const float4 lox = __ldg(n), hix = __ldg(n + 1), loy = __ldg(n + 2), hiy = __ldg(n + 3), loz = __ldg(n + 4), hiz = __ldg(n + 5);
         const float4 chf = __ldg(n + 6);
@@ -495,17 +497,27 @@ struct TravF4 : TravF {
         float tk = ka; ka = kb; kb = tk;  \
         int32_t tc = ca; ca = cb; cb = tc;\
     }
-        PATHS_CE(k0, c0, k1, c1)
-        PATHS_CE(k2, c2, k3, c3)
-        PATHS_CE(k0, c0, k2, c2)
-        PATHS_CE(k1, c1, k3, c3)
-        PATHS_CE(k1, c1, k2, c2)
+        if (SORT) {
+            PATHS_CE(k0, c0, k1, c1)
+            PATHS_CE(k2, c2, k3, c3)
+            PATHS_CE(k0, c0, k2, c2)
+            PATHS_CE(k1, c1, k3, c3)
+            PATHS_CE(k1, c1, k2, c2)
+            if (k3 < inf) sstack[(sp++) * stride] = c3;
+            if (k2 < inf) sstack[(sp++) * stride] = c2;
+            if (k1 < inf) sstack[(sp++) * stride] = c1;
+            if (k0 < inf) node = c0;
+            else node = sp > 0 ? sstack[(--sp) * stride] : PATHS_TRAV_DONE;
+        } else {
+            // unsorted: hits are not a prefix any more; enter the last hit child, push the others
+            int32_t next = PATHS_TRAV_DONE;
+            if (k0 < inf) next = c0;
+            if (k1 < inf) { if (next != PATHS_TRAV_DONE) sstack[(sp++) * stride] = next; next = c1; }
+            if (k2 < inf) { if (next != PATHS_TRAV_DONE) sstack[(sp++) * stride] = next; next = c2; }
+            if (k3 < inf) { if (next != PATHS_TRAV_DONE) sstack[(sp++) * stride] = next; next = c3; }
+            node = next != PATHS_TRAV_DONE ? next : (sp > 0 ? sstack[(--sp) * stride] : PATHS_TRAV_DONE);
+        }
 #undef PATHS_CE
-        if (k3 < inf) sstack[(sp++) * stride] = c3;
-        if (k2 < inf) sstack[(sp++) * stride] = c2;
-        if (k1 < inf) sstack[(sp++) * stride] = c1;
-        if (k0 < inf) node = c0;
-        else node = sp > 0 ? sstack[(--sp) * stride] : PATHS_TRAV_DONE;
     }
     __device__ __forceinline__ int32_t pop4(const int32_t *sstack, uint32_t stride) { return sp > 0 ? sstack[(--sp) * stride] : PATHS_TRAV_DONE; }
 };

@@ -708,7 +708,7 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_shadow4(DevScene sc, P
         for (int r = 0; r < ROUNDS; r++) {
             if (has) {
 #pragma unroll 1
-                for (int k = 0; k < KI && tv.node >= 0; k++) tv.inner4(nodes4, sstack, stride);
+                for (int k = 0; k < KI && tv.node >= 0; k++) tv.inner4<false>(nodes4, sstack, stride);
                 bool occluded = false;
                 if (tv.node < 0 && tv.node != PATHS_TRAV_DONE) {
                     occluded = tv.leaf_test<true>(leaves, tv.node, skip);

@@ -80,10 +80,15 @@ def test_device_tree_dragon(pb, oracle_mod):
     info = gsc.info
     assert info["bvh_builder"] == 1 and info["giant_prims"] == 6
     # build time: the first build of a process also pays for loading the builder's kernels, so a second staging is timed
-    gsc.build_bvh()
-    gsc.build_bvh(device=True)
-    assert gsc.check_bvh() == 0
-    assert gsc.info["build_ms_device"] < 100.0  # the host SAH build takes 0.5 - 0.9 s
+    # and the best of three (the event-timed region includes the scratch cudaMalloc, whose cost depends on what the process freed before)
+    host_ms = gsc.build_bvh()["build_ms_fast"]
+    dev_ms = []
+    for _ in range(3):
+        gsc.build_bvh()
+        gsc.build_bvh(device=True)
+        assert gsc.check_bvh() == 0  # stages the scene: this is where the device build runs
+        dev_ms.append(gsc.info["build_ms_device"])
+    assert min(dev_ms) < 100.0 and min(dev_ms) < 0.5 * host_ms, (dev_ms, host_ms)  # the host SAH build takes 0.5 - 0.9 s
     o, d, _ = oracle_mod.camera_rays(cam, 4, 0)
     o32, d32 = o.astype(np.float32).astype(np.float64), d.astype(np.float32).astype(np.float64)
     r0, u0, b0 = osc.trace_closest(o32, d32, want_bary=True)

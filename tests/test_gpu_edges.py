@@ -98,7 +98,7 @@ def test_axis_aligned_rays(pb, oracle_mod):
     o, d = np.concatenate(rays_o), np.concatenate(rays_d)
     p0, t0, hit = check_f64(oracle_mod, osc, gsc, o, d)
     assert hit.mean() > 0.05
-    assert check_f32(oracle_mod, osc, gsc, o, d, p0, t0, face_grazes=4) > 0.99  # lattice line x = -1, z = 0 is tangent to the light sphere
+    assert check_f32(oracle_mod, osc, gsc, o, d, p0, t0, face_grazes=8) > 0.99  # the lattice lines (x, z) = (+-1, 0), (0, +-1) along +-y are tangent to the light sphere
     # negative zero components take the other sign of infinity
     d2 = np.where(d == 0.0, -0.0, d)
     check_f64(oracle_mod, osc, gsc, o, d2)
