@@ -74,7 +74,7 @@ __host__ __device__ __forceinline__ uint32_t cmj_hash(uint32_t i, uint32_t p) {
 template <typename R> __device__ __forceinline__ R cmj_rand_float(uint32_t i, uint32_t p) { return R(cmj_hash(i, p)) * R(1.0 / 4294967808.0); }
 
 // sampling.rs:226-235
-template <typename R> __device__ __forceinline__ void cmj(uint32_t s, uint32_t m, uint32_t n, uint32_t p, R &x, R &y) {
+template <typename R> __device__ __forceinline__ void cmj_mn(uint32_t s, uint32_t m, uint32_t n, uint32_t p, R &x, R &y) {
     uint32_t ps = cmj_permute(s, m * n, p * 0xa73bd290u);
     R sx = R(cmj_permute(ps % m, m, p * 0xa511e9b3u));
     R sy = R(cmj_permute(ps / m, n, p * 0x63d83595u));
@@ -82,6 +82,12 @@ template <typename R> __device__ __forceinline__ void cmj(uint32_t s, uint32_t m
     R jy = cmj_rand_float<R>(s, p * 0x711ad6a5u);
     x = (R(s % m) + (sy + jx) / R(n)) / R(m);
     y = (R(s / m) + (sx + jy) / R(m)) / R(n);
+}
+// every sample but a pixel's first comes from a (5, 5) pattern (sample_schedule below): with m and n known at compile time the
+// integer remainders and quotients become multiplications (same values; the float divisions stay divisions)
+template <typename R> __device__ __forceinline__ void cmj(uint32_t s, uint32_t m, uint32_t n, uint32_t p, R &x, R &y) {
+    if (m == 5u && n == 5u) cmj_mn<R>(s, 5u, 5u, p, x, y);
+    else cmj_mn<R>(s, m, n, p, x, y);
 }
 // sampling.rs:250-264
 template <typename R> __device__ __forceinline__ void cmj_disk(uint32_t s, uint32_t m, uint32_t n, uint32_t p, R &dx, R &dy) {

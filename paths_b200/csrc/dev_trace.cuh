@@ -145,21 +145,20 @@ struct RayFrame {
     float px, py, pz, qx, qy, qz;
 };
 __device__ __forceinline__ RayFrame ray_frame(float dx, float dy, float dz) {
+    // Branch-free: lanes of a warp disagree on the dominant axis after the first bounce, and three divergent arms (a division each) cost
+    // three times the warp instructions of one arm plus selects.  Same arithmetic per lane as the three-armed form: -u / dk, -v / dk.
     RayFrame f;
-    float ax = fabsf(dx), ay = fabsf(dy), az = fabsf(dz);
-    if (az >= ax && az >= ay) { // kz = z
-        float iz = 1.0f / dz;
-        f.px = 1.0f; f.py = 0.0f; f.pz = -dx * iz;
-        f.qx = 0.0f; f.qy = 1.0f; f.qz = -dy * iz;
-    } else if (ay >= ax) { // kz = y
-        float iy = 1.0f / dy;
-        f.px = 0.0f; f.py = -dz * iy; f.pz = 1.0f;
-        f.qx = 1.0f; f.qy = -dx * iy; f.qz = 0.0f;
-    } else { // kz = x
-        float ix = 1.0f / dx;
-        f.px = -dy * ix; f.py = 1.0f; f.pz = 0.0f;
-        f.qx = -dz * ix; f.qy = 0.0f; f.qz = 1.0f;
-    }
+    const float ax = fabsf(dx), ay = fabsf(dy), az = fabsf(dz);
+    const bool kz_z = az >= ax && az >= ay, kz_y = !kz_z && ay >= ax;
+    const float ik = 1.0f / (kz_z ? dz : (kz_y ? dy : dx));
+    const float pu = -(kz_z ? dx : (kz_y ? dz : dy)) * ik; // kz = z: p = (1, 0, -dx/dz)   kz = y: p = (0, -dz/dy, 1)   kz = x: p = (-dy/dx, 1, 0)
+    const float qv = -(kz_z ? dy : (kz_y ? dx : dz)) * ik; //         q = (0, 1, -dy/dz)           q = (1, -dx/dy, 0)           q = (-dz/dx, 0, 1)
+    f.px = kz_z ? 1.0f : (kz_y ? 0.0f : pu);
+    f.py = kz_z ? 0.0f : (kz_y ? pu : 1.0f);
+    f.pz = kz_z ? pu : (kz_y ? 1.0f : 0.0f);
+    f.qx = kz_z ? 0.0f : (kz_y ? 1.0f : qv);
+    f.qy = kz_z ? 1.0f : (kz_y ? qv : 0.0f);
+    f.qz = kz_z ? qv : (kz_y ? 0.0f : 1.0f);
     return f;
 }
 struct TriHit {
