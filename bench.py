@@ -374,6 +374,11 @@ def run_ours(args, rank, world, local_rank):
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic, "traffic_source": traffic_src,
                          "kernel": "closest-hit kernels: k_camera_extend (raygen + camera segment) and k_extend_refill<1,16,8> (bounces)", "launches": int(n_ext_launch), "avg_launch_ms": ext_ms / n_ext_launch,
                          "algorithmic_bytes_per_ray": Q, "algorithmic_bytes_per_sample": per_sample,
+                         # the physical side: measured DRAM bytes per launch over the live launch time -- what HBM really carries
+                         "dram_gbs_measured": (traffic / (ext_ms / n_ext_launch * 1e-3) / 1e9) if traffic and ext_ms > 0 else None,
+                         "dram_frac_measured": (traffic / (ext_ms / n_ext_launch * 1e-3) / 1e9 / peak) if traffic and ext_ms > 0 else None,
+                         "limiter": "issue slots and SIMT divergence (ncu: 72-81 % issue-active, 12.7 of 32 lanes on bounce rays, 24 of 32 on camera "
+                                    "rays; profiles/r01e_extend_teapot_summary.txt, r01e_camera_teapot_summary.txt), not HBM",
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst)" if peaks else "fallback 6650",
                          "kernel_share_of_step": ext_ms / max(dt_["ms_total"], 1e-9),
                          "split_ms": {k: dt_[k] for k in ("ms_raygen", "ms_extend", "ms_shade", "ms_shadow", "ms_accumulate")},
