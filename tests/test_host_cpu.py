@@ -262,3 +262,14 @@ def test_hdr_rle_roundtrip(pb, oracle_mod, tmp_path):
         y.write_text((ROOT / "scenes" / "spheres_on_plane.yml").read_text().split("skybox:")[0] + f"skybox:\n  type: Hdri\n  filename: {tmp_path}/{f}\n"
                      + "objects:" + (ROOT / "scenes" / "spheres_on_plane.yml").read_text().split("objects:")[1])
         assert pb.Scene.load(str(y)).info["n_prims"] == 4
+
+
+def test_abi_rejects_null_and_out_of_range_arguments():
+    # the reference panics on bad input (renderer.rs:88,107-109; scene.rs:188); the C ABI must neither unwind nor fault
+    import subprocess
+    import sys
+
+    r = subprocess.run([sys.executable, str(ROOT / "tests" / "abi_null_probe.py")], cwd=ROOT, capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "UNEXPECTED OK: []" in r.stdout
+    assert r.stdout.count("-> 1 ") >= 40  # PATHS_ERR_INVALID_ARG with a message each
