@@ -1,4 +1,5 @@
-"""Calls every C-ABI entry point with NULL handles / NULL outputs / out-of-range ids (run as a subprocess by test_host_cpu.py so that a\ncrash shows up as a failed test): each must return a paths_status error and set paths_last_error(), none may succeed or fault."""
+"""Calls every C-ABI entry point with NULL handles / NULL outputs / out-of-range ids (run as a subprocess by test_host_cpu.py so that a
+crash shows up as a failed test): each must return a paths_status error and set paths_last_error(), none may succeed or fault."""
 import ctypes as C, sys
 sys.path.insert(0, str(__import__('pathlib').Path(__file__).resolve().parent.parent))
 import paths_b200 as pb
