@@ -89,3 +89,56 @@ def test_missing_asset_and_missing_scene(tmp_path):
     with pytest.raises(pb.PathsError):
         pb.Scene.load(str(tmp_path / "nope.yml"))
     assert os.path.exists(yml)
+
+
+HDR_SCENE = textwrap.dedent("""\
+    camera:
+      image_width: 16
+      image_height: 8
+      location: {{ x: 0.0, y: 1.0, z: -5.0 }}
+      orientation: {{ pitch: 0.0, yaw: 0.0, roll: 0.0 }}
+      sensor_width: 0.036
+      sensor_height: 0.024
+      focal_length: 0.05
+      focus_distance: 5.0
+      aperture: 8.0
+    skybox:
+      type: Hdri
+      filename: "{hdr}"
+    models: {{}}
+    lights: []
+    objects:
+      - shape:
+          type: Sphere
+          radius: 1.0
+          center: {{ x: 0.0, y: 1.0, z: 0.0 }}
+        material:
+          type: Mirror
+    """)
+HDR_HEAD = b"#?RADIANCE\nFORMAT=32-bit_rle_rgbe\n\n-Y 2 +X 8\n"
+HDR_CASES = {
+    "good.hdr": (HDR_HEAD + bytes([128, 128, 128, 129]) * 16, True),
+    "short_flat.hdr": (HDR_HEAD + bytes([128, 128, 128, 129]) * 9, False),
+    "rle_overrun.hdr": (HDR_HEAD + bytes([2, 2, 0, 8]) + bytes([128 + 100, 7]) * 4, False),  # a run longer than the scanline
+    "rle_truncated.hdr": (HDR_HEAD + bytes([2, 2, 0, 8]) + bytes([128 + 8, 7]), False),
+    "no_resolution.hdr": (b"#?RADIANCE\nFORMAT=32-bit_rle_rgbe\n\n", False),
+    "bad_magic.hdr": (b"P6\n8 2\n255\n" + bytes(48), False),
+    "zero_size.hdr": (b"#?RADIANCE\nFORMAT=32-bit_rle_rgbe\n\n-Y 0 +X 0\n", False),
+    "empty.hdr": (b"", False),
+}
+
+
+@pytest.mark.parametrize("name", sorted(HDR_CASES))
+def test_malformed_hdr_returns_a_status(tmp_path, name):
+    import paths_b200 as pb
+
+    data, ok = HDR_CASES[name]
+    hdr = tmp_path / name
+    hdr.write_bytes(data)
+    yml = tmp_path / (name + ".yml")
+    yml.write_text(HDR_SCENE.format(hdr=str(hdr)))
+    if ok:
+        assert pb.Scene.load(str(yml)).info["n_prims"] == 1
+    else:
+        with pytest.raises(pb.PathsError):
+            pb.Scene.load(str(yml))
