@@ -121,6 +121,9 @@ typedef struct paths_renderer paths_renderer;
 /* ------------------------------------------------------------------ options */
 
 enum { PATHS_PRECISION_AUTO = 0, PATHS_PRECISION_F32 = 32, PATHS_PRECISION_MIXED = 48, PATHS_PRECISION_F64 = 64 };
+/* f32 traversal kernels the per-ray seam can be pointed at (precision argument of paths_trace_closest / paths_trace_occluded);
+ * PATHS_PRECISION_F32 itself means "whatever a render of this scene launches for bounce and visibility rays" */
+enum { PATHS_TRACE_CAMERA = 33, PATHS_TRACE_TWO_WIDE = 34, PATHS_TRACE_PLAIN = 35, PATHS_TRACE_FOUR_WIDE = 36 };
 enum { PATHS_SHARD_SAMPLES = 0, PATHS_SHARD_TILES = 1 };
 enum { PATHS_BVH_FAST = 0, PATHS_BVH_REFERENCE = 1, PATHS_BVH_DEVICE = 2 };
 /* Estimator extensions that have NO reference behaviour; all off by default so that output stays in parity.
@@ -157,6 +160,13 @@ typedef struct {
     double ms_raygen, ms_extend, ms_shade, ms_shadow, ms_accumulate, ms_total; /* valid with time_kernels */
     uint64_t n_extend_launches, n_shadow_launches;
     double ms_device; /* device time of all render calls since reset: CUDA events on the launching stream, first to last kernel */
+    /* two-wide traversal stack overflows on this device since the library was loaded (a dropped subtree = a possibly missed hit);
+     * both tree builders bound the depth so that this stays 0, and the ray-level tests assert it */
+    uint64_t stack_overflows;
+    /* which kernels this renderer launches: extend / visibility kernel for bounce rays (0 plain batches, 3 two-wide lane refill,
+     * 16 four-wide), camera segment (1 = raygen fused with a plain-batch closest hit), shade scheduling (1 static round-robin,
+     * 0 dynamic fetch), pass contexts in flight */
+    int32_t extend_kernel, camera_kernel, shade_kernel, pass_contexts;
 } paths_stats;
 
 typedef struct {
@@ -212,9 +222,23 @@ paths_status paths_scene_prim_entity(const paths_scene *s, uint32_t prim, int32_
 
 /* BVH::find_intersection over a batch of host rays (src/bvh.rs:78-140).  prim_id = PATHS_MISS and t = +inf on a miss.
  * precision 64: reference-order binary tree, f64, reference operation order (bit-exact ids and t);
- * precision 32: production wide tree, f32 triangles / f64 spheres.  bary (n x 3) may be NULL. */
+ * precision 48: production tree, f32 box tests, the reference's f64 primitive tests (mixed mode);
+ * precision 32: the PRODUCTION closest-hit kernel: the rays are staged into a path-state buffer and traced by the very kernel, node
+ *   layout and grid a render of this scene launches for its bounce rays (k_extend_refill over two-wide nodes up to 64k primitives,
+ *   k_extend4s over four-wide nodes above); f32 boxes and watertight f32 triangles, f64 spheres;
+ * PATHS_TRACE_CAMERA: the routine the fused camera kernel runs on primary rays (plain batches of 32 over two-wide nodes);
+ * PATHS_TRACE_TWO_WIDE / _FOUR_WIDE / _PLAIN: one of the f32 kernels regardless of the scene's size.
+ * bary (n x 3) may be NULL. */
 paths_status paths_trace_closest(paths_scene *s, int32_t device, const double *origins, const double *dirs, size_t n,
                                  uint32_t *prim_id, double *t, double *bary, int32_t precision);
+/* The shadow query of trace_ray (src/trace.rs:61-66: closest hit, then `entity != light`) over a batch of host rays, through the
+ * visibility kernel a render launches (precision 32: k_shadow_refill / k_shadow4 -- any-hit with the nearest hit on the light's own
+ * sphere as the search bound; 48: the same predicate with f64 primitives; 64: the reference's closest-hit-then-compare rule on its
+ * own tree; PATHS_TRACE_* codes as above).  light[i] = index of the light ray i was sampled toward (hits on that light do not
+ * occlude), or NULL: every hit occludes.  occluded[i] = 1 blocked, 0 clear (the kernel added the record's contribution to its path's
+ * radiance exactly once). */
+paths_status paths_trace_occluded(paths_scene *s, int32_t device, const double *origins, const double *dirs, const uint32_t *light,
+                                  size_t n, uint8_t *occluded, int32_t precision);
 
 /* ------------------------------------------------------------------ renderer (replaces Renderer, src/renderer.rs:33-141) */
 

@@ -11,7 +11,7 @@ import ctypes as C
 import numpy as np
 
 from . import _capi
-from ._capi import (EXT_ENV_NEE, EXT_GGX, EXT_MICROFACET, EXT_MICROFACET_COSINE, EXT_NEE_ALL_LIGHTS, MISS, PRECISION_AUTO, PRECISION_F32, PRECISION_F64, PRECISION_MIXED, SHARD_SAMPLES, SHARD_TILES, Camera, PathsError,  # noqa: F401
+from ._capi import (TRACE_CAMERA, TRACE_FOUR_WIDE, TRACE_PLAIN, TRACE_TWO_WIDE, EXT_ENV_NEE, EXT_GGX, EXT_MICROFACET, EXT_MICROFACET_COSINE, EXT_NEE_ALL_LIGHTS, MISS, PRECISION_AUTO, PRECISION_F32, PRECISION_F64, PRECISION_MIXED, SHARD_SAMPLES, SHARD_TILES, Camera, PathsError,  # noqa: F401
                     RenderOpts, SceneInfo, Stats, build, check, lib)
 
 __all__ = ["Scene", "Renderer", "Image", "Camera", "PathsError", "build", "lib", "camera_rays", "device_count", "MISS"]
@@ -200,6 +200,19 @@ class Scene:
         bary = np.empty((n, 3), dtype=np.float64) if want_bary else None
         check(lib().paths_trace_closest(self._h, device, _p(o), _p(d), n, _p(prim), _p(t), _p(bary) if want_bary else None, precision))
         return (prim, t, bary) if want_bary else (prim, t)
+
+    def occluded(self, origins, dirs, light=None, precision=PRECISION_F32, device=0):
+        """The shadow query of trace_ray (src/trace.rs:61-66) over a batch of rays, through the visibility kernel a render launches.
+        light: index (or per-ray indices) of the light the rays were sampled toward, None = every hit occludes.  -> uint8 flags."""
+        o = np.ascontiguousarray(origins, dtype=np.float64).reshape(-1, 3)
+        d = np.ascontiguousarray(dirs, dtype=np.float64).reshape(-1, 3)
+        n = o.shape[0]
+        lt = None
+        if light is not None:
+            lt = np.ascontiguousarray(np.broadcast_to(np.asarray(light, dtype=np.uint32), (n,)))
+        occ = np.empty(n, dtype=np.uint8)
+        check(lib().paths_trace_occluded(self._h, device, _p(o), _p(d), _p(lt) if lt is not None else None, n, _p(occ), precision))
+        return occ
 
 
 class Renderer:

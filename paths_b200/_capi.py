@@ -15,6 +15,7 @@ LIB_PATH = _PKG / "lib" / "libpaths_b200.so"
 OK, ERR_INVALID_ARG, ERR_IO, ERR_PARSE, ERR_CUDA, ERR_UNSUPPORTED, ERR_INTERNAL = range(7)
 MISS = 0xFFFFFFFF
 PRECISION_AUTO, PRECISION_F32, PRECISION_MIXED, PRECISION_F64 = 0, 32, 48, 64
+TRACE_CAMERA, TRACE_TWO_WIDE, TRACE_PLAIN, TRACE_FOUR_WIDE = 33, 34, 35, 36  # f32 kernels the per-ray seam can be pointed at
 SHARD_SAMPLES, SHARD_TILES = 0, 1
 EXT_ENV_NEE, EXT_MICROFACET, EXT_MICROFACET_COSINE, EXT_GGX, EXT_NEE_ALL_LIGHTS = 1, 2, 4, 8, 16
 MAT_TYPES = {"Lambertian": 0, "Mirror": 1, "Gloss": 2, "CookTorrance": 3, "Fresnel": 4}
@@ -80,7 +81,8 @@ class Stats(C.Structure):
                 ("kernel_launches", C.c_uint64), ("passes", C.c_uint64), ("ms_raygen", C.c_double), ("ms_extend", C.c_double),
                 ("ms_shade", C.c_double), ("ms_shadow", C.c_double), ("ms_accumulate", C.c_double), ("ms_total", C.c_double),
                 ("n_extend_launches", C.c_uint64), ("n_shadow_launches", C.c_uint64),
-                ("ms_device", C.c_double)]
+                ("ms_device", C.c_double), ("stack_overflows", C.c_uint64), ("extend_kernel", C.c_int32), ("camera_kernel", C.c_int32),
+                ("shade_kernel", C.c_int32), ("pass_contexts", C.c_int32)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -118,6 +120,7 @@ SIGNATURES = {
     "paths_scene_prim_geometry": (C.c_int, [VP, C.c_uint32, VP, C.POINTER(C.c_int32)]),
     "paths_scene_prim_entity": (C.c_int, [VP, C.c_uint32, C.POINTER(C.c_int32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
     "paths_trace_closest": (C.c_int, [VP, C.c_int32, VP, VP, C.c_size_t, VP, VP, VP, C.c_int32]),
+    "paths_trace_occluded": (C.c_int, [VP, C.c_int32, VP, VP, VP, C.c_size_t, VP, C.c_int32]),
     "paths_render_opts_default": (None, [C.POINTER(RenderOpts)]),
     "paths_renderer_create": (C.c_int, [VP, C.POINTER(Camera), C.POINTER(RenderOpts), C.POINTER(VP)]),
     "paths_renderer_render": (C.c_int, [VP, C.c_uint32]),

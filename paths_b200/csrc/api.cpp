@@ -129,6 +129,16 @@ void retire_fast_staged(paths_scene *s) {
     s->staged.swap(keep);
 }
 
+// PATHS_TRACE_* codes name one f32 kernel: (precision F32, kernel code); everything else has kernel 0 (the render's own choice)
+int trace_kernel_of(int32_t &precision) {
+    if (precision == PATHS_TRACE_CAMERA || precision == PATHS_TRACE_TWO_WIDE || precision == PATHS_TRACE_PLAIN || precision == PATHS_TRACE_FOUR_WIDE) {
+        int k = precision;
+        precision = PATHS_PRECISION_F32;
+        return k;
+    }
+    return 0;
+}
+
 int resolve_precision(const paths_scene *s, int32_t precision) {
     if (precision == PATHS_PRECISION_F32 || precision == PATHS_PRECISION_F64 || precision == PATHS_PRECISION_MIXED) return precision;
     return s->hs.auto_precision;
@@ -544,6 +554,7 @@ paths_status paths_trace_closest(paths_scene *s, int32_t device, const double *o
     if (!s || (n && (!origins || !dirs || !prim_id || !t))) return fail(PATHS_ERR_INVALID_ARG, "null argument");
     paths_status st = check_device(device);
     if (st != PATHS_OK) return st;
+    const int kernel = trace_kernel_of(precision);
     int prec = resolve_precision(s, precision);
     const SceneDevice *sd = nullptr;
     st = ensure_staged(s, device, prec == PATHS_PRECISION_F64, prec != PATHS_PRECISION_F64, &sd);
@@ -551,7 +562,30 @@ paths_status paths_trace_closest(paths_scene *s, int32_t device, const double *o
     std::string err;
     st = prec == PATHS_PRECISION_F64     ? trace_closest_f64(sd, origins, dirs, n, prim_id, t, bary, err)
          : prec == PATHS_PRECISION_MIXED ? trace_closest_mixed(sd, origins, dirs, n, prim_id, t, bary, err)
-                                         : trace_closest_f32(sd, origins, dirs, n, prim_id, t, bary, err);
+                                         : trace_closest_f32(sd, origins, dirs, n, prim_id, t, bary, kernel, err);
+    return st == PATHS_OK ? st : fail(st, err);
+    PATHS_GUARD_END
+}
+
+paths_status paths_trace_occluded(paths_scene *s, int32_t device, const double *origins, const double *dirs, const uint32_t *light, size_t n,
+                                  uint8_t *occluded, int32_t precision) {
+    PATHS_GUARD_BEGIN
+    if (!s || (n && (!origins || !dirs || !occluded))) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    if (light)
+        for (size_t i = 0; i < n; i++)
+            if (light[i] >= s->hs.lights.size()) return fail(PATHS_ERR_INVALID_ARG, "light index out of range");
+    paths_status st = check_device(device);
+    if (st != PATHS_OK) return st;
+    const int kernel = trace_kernel_of(precision);
+    if (kernel == PATHS_TRACE_CAMERA) return fail(PATHS_ERR_INVALID_ARG, "PATHS_TRACE_CAMERA names a closest-hit routine; visibility rays never run it");
+    int prec = resolve_precision(s, precision);
+    const SceneDevice *sd = nullptr;
+    st = ensure_staged(s, device, prec == PATHS_PRECISION_F64, prec != PATHS_PRECISION_F64, &sd);
+    if (st != PATHS_OK) return st;
+    std::string err;
+    st = prec == PATHS_PRECISION_F64     ? trace_occluded_f64(sd, origins, dirs, light, n, occluded, err)
+         : prec == PATHS_PRECISION_MIXED ? trace_occluded_mixed(sd, origins, dirs, light, n, occluded, err)
+                                         : trace_occluded_f32(sd, origins, dirs, light, n, occluded, kernel, err);
     return st == PATHS_OK ? st : fail(st, err);
     PATHS_GUARD_END
 }

@@ -105,10 +105,12 @@ template <typename R4> struct PathState {
     R4 *sh_c;  // contribution rgb (already multiplied by throughput)
 };
 
+#define PATHS_NWORK 4
 struct PassControl {
     uint32_t *qcount;    // [max_bounces + 2] live paths entering bounce b
     uint32_t *scount;    // [max_bounces + 2] shadow rays emitted at bounce b
-    uint32_t *work;      // [3 * (max_bounces + 2)] dynamic-fetch cursors, one per launch
+    uint32_t *ecount;    // [max_bounces + 2] environment NEE records emitted at bounce b (extension; second half of the shadow arrays)
+    uint32_t *work;      // [PATHS_NWORK * (max_bounces + 2)] dynamic-fetch cursors, one per launch: extend, shade, shadow, env shadow
     uint32_t *queue[2];  // slot indices, ping-pong
     unsigned long long *totals; // [0] extend rays [1] shadow rays [2] bad samples [3] samples
 };

@@ -75,6 +75,18 @@ template <typename R> __device__ __forceinline__ R beckmann_ndf(R m, V3<R> n, V3
     R d0 = e / (Consts<R>::pi() * m * m * pow_(cos_alpha, R(4.0)));
     return fmax_(R(0.0), d0 * dot(n, h));
 }
+// Production (f32): h and n are normalised with rsqrtf (about 2 ulp each), so their dot product can exceed 1 at the centre of a
+// highlight and acosf would return NaN.  Same function without the inverse trigonometry: cos(alpha) = c clamped to [-1, 1],
+// tan^2(alpha) = (1 - c^2) / c^2.
+template <> __device__ __forceinline__ float beckmann_ndf<float>(float m, V3<float> n, V3<float> h) {
+    float c = fminf(1.0f, fmaxf(-1.0f, dot(h, n)));
+    float c2 = c * c;
+    if (!(c2 > 0.0f)) return 0.0f;
+    float tan2 = (1.0f - c2) / c2;
+    float e = expf(-tan2 / (m * m));
+    float d0 = e / (Consts<float>::pi() * m * m * c2 * c2);
+    return fmaxf(0.0f, d0 * c);
+}
 // extension: the GGX / Trowbridge-Reitz distribution in the same D * (n.h) form as ct_ndf above
 template <typename R> __device__ __forceinline__ R ggx_ndf(R m, V3<R> n, V3<R> h) {
     R c = dot(n, h);

@@ -199,6 +199,14 @@ struct HitF {
 };
 
 #define PATHS_FAST_STACK 64
+// A two-wide traversal holds at most one postponed sibling per tree level, and both builders refuse trees deeper than 60 levels
+// (bvh_fast.cpp, bvh_device.cu), so the 64-entry stack cannot overflow.  Should it ever, the subtree is dropped AND counted here:
+// paths_stats.stack_overflows reports the total and the ray-level tests assert it is zero.  One copy per translation unit and device.
+static __device__ unsigned long long g_stack_overflows = 0ull;
+__device__ __forceinline__ void stack_push(int32_t *stack, int &sp, int32_t v) {
+    if (sp < PATHS_FAST_STACK) stack[sp++] = v;
+    else atomicAdd(&g_stack_overflows, 1ull);
+}
 
 // ANY = true: return as soon as any primitive other than `skip_prim` is hit closer than tmax (shadow rays).
 template <bool ANY> __device__ __forceinline__ HitF trace_fast(const DevScene &sc, float ox, float oy, float oz, float dx, float dy, float dz,
@@ -238,7 +246,7 @@ template <bool ANY> __device__ __forceinline__ HitF trace_fast(const DevScene &s
             if (h0 && h1) {
                 bool first0 = tn0 <= tn1;
                 node = first0 ? c0 : c1;
-                if (sp < PATHS_FAST_STACK) stack[sp++] = first0 ? c1 : c0;
+                stack_push(stack, sp, first0 ? c1 : c0);
             } else if (h0) node = c0;
             else if (h1) node = c1;
             else {
@@ -332,7 +340,7 @@ template <bool ANY> __device__ __forceinline__ Hit64 trace_mixed(const DevScene 
             if (h0 && h1) {
                 bool first0 = tn0 <= tn1;
                 node = first0 ? c0 : c1;
-                if (sp < PATHS_FAST_STACK) stack[sp++] = first0 ? c1 : c0;
+                stack_push(stack, sp, first0 ? c1 : c0);
             } else if (h0) node = c0;
             else if (h1) node = c1;
             else {
@@ -409,7 +417,7 @@ struct TravF {
         if (h0 && h1) {
             bool first0 = tn0 <= tn1;
             node = first0 ? c0 : c1;
-            if (sp < PATHS_FAST_STACK) stack[sp++] = first0 ? c1 : c0;
+            stack_push(stack, sp, first0 ? c1 : c0);
         } else if (h0) node = c0;
         else if (h1) node = c1;
         else node = sp > 0 ? stack[--sp] : PATHS_TRAV_DONE;

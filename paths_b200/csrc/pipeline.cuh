@@ -301,8 +301,17 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
             if (EXT && (ext & PATHS_EXT_NEE_ALL_LIGHTS)) direct = direct * R(nl); // extension: undo the uniform light choice
             if (col_bad(direct)) atomicAdd(totals + 2, 1ull); // Colour::check (trace.rs:80)
             V3<R> contrib = direct * throughput;
+            // production instantiation: a NaN contribution (the reference's Colour::check lets NaN through, colour.rs:56-60, and the
+            // pixel stays NaN for the whole epoch) is counted as a bad sample and dropped; the f64 instantiation follows the reference
+            bool usable = true;
+            if constexpr (!IsF64<R>::value) {
+                if (isnan_(contrib.x) || isnan_(contrib.y) || isnan_(contrib.z)) {
+                    atomicAdd(totals + 2, 1ull);
+                    usable = false;
+                }
+            }
             // a zero contribution cannot change the estimate: skip its visibility query
-            if (contrib.x != R(0) || contrib.y != R(0) || contrib.z != R(0)) {
+            if (usable && (contrib.x != R(0) || contrib.y != R(0) || contrib.z != R(0))) {
                 out.shadow = true;
                 out.sh_o = new_origin;
                 out.sh_d = sdir;
@@ -362,8 +371,8 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
 template <typename R, bool LIGHTS, bool EXT>
 __global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LIGHTS || EXT) ? PATHS_LB_SHADE : PATHS_LB_SHADE_PLAIN)) k_shade(DevScene sc, PathState<typename Vec4T<R>::type> ps, ShardInfo shard, uint32_t s_base, uint32_t k0,
                                                uint32_t k1, uint32_t max_bounces, uint32_t ext, const uint32_t *queue, uint32_t *queue_next,
-                                               const uint32_t *count_ptr, uint32_t *next_count, uint32_t *shadow_count, uint32_t *cursor,
-                                               unsigned long long *totals) {
+                                               const uint32_t *count_ptr, uint32_t *next_count, uint32_t *shadow_count, uint32_t *env_count,
+                                               uint32_t env_base, uint32_t *cursor, unsigned long long *totals) {
     const uint32_t count = *count_ptr;
     const uint32_t lane = threadIdx.x & 31u;
     // cursor == nullptr: batches of 32 entries are dealt to the warps of the grid round-robin (shading cost per entry is
@@ -427,7 +436,9 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LI
             }
         }
         if (EXT && (ext & PATHS_EXT_ENV_NEE)) { // warp-uniform
-            uint32_t epos = warp_append(shadow_count, out.shadow2);
+            // environment records go to the second half of the shadow arrays with a counter of their own; a launch of its own resolves
+            // them after the light records (two records of one slot in one launch would race on the slot's radiance record)
+            uint32_t epos = env_base + warp_append(env_count, out.shadow2);
             if (out.shadow2) {
                 ps.sh_o[epos] = mk4(out.sh_o.x, out.sh_o.y, out.sh_o.z, bits_to_real(PATHS_LIGHT_ENV, R(0)));
                 ps.sh_d[epos] = mk4(out.sh2_d.x, out.sh2_d.y, out.sh2_d.z, bits_to_real(slot, R(0)));
@@ -530,7 +541,7 @@ __global__ void __launch_bounds__(128) k_shadow(DevScene sc, PathState<typename 
                 col.x += c.x;
                 col.y += c.y;
                 col.z += c.z;
-                if (col.x < R(0) || col.y < R(0) || col.z < R(0)) atomicAdd(totals + 2, 1ull); // Colour::check (trace.rs:82)
+                if (!(col.x >= R(0) && col.y >= R(0) && col.z >= R(0))) atomicAdd(totals + 2, 1ull); // Colour::check (trace.rs:82); NaN counts
                 st_rec(&ps.col[slot], col);
             }
         }
@@ -646,7 +657,7 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_shadow_refill(DevScene
                     float4 c = ld_rec(&ps.sh_c[rec]);
                     float4 col = ld_rec(&ps.col[slot]);
                     col.x += c.x; col.y += c.y; col.z += c.z;
-                    if (col.x < 0.0f || col.y < 0.0f || col.z < 0.0f) atomicAdd(totals + 2, 1ull);
+                    if (!(col.x >= 0.0f && col.y >= 0.0f && col.z >= 0.0f)) atomicAdd(totals + 2, 1ull);
                     st_rec(&ps.col[slot], col);
                     has = false;
                 }
@@ -719,7 +730,7 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_shadow4(DevScene sc, P
                     float4 c = ld_rec(&ps.sh_c[rec]);
                     float4 col = ld_rec(&ps.col[slot]);
                     col.x += c.x; col.y += c.y; col.z += c.z;
-                    if (col.x < 0.0f || col.y < 0.0f || col.z < 0.0f) atomicAdd(totals + 2, 1ull);
+                    if (!(col.x >= 0.0f && col.y >= 0.0f && col.z >= 0.0f)) atomicAdd(totals + 2, 1ull);
                     st_rec(&ps.col[slot], col);
                     has = false;
                 }
@@ -825,7 +836,7 @@ template <typename R> __global__ void k_tally(PassControl pc, uint32_t n_bounces
         unsigned long long e = 0, s = 0;
         for (uint32_t b = 0; b < n_bounces; b++) {
             e += pc.qcount[b];
-            s += pc.scount[b];
+            s += pc.scount[b] + pc.ecount[b];
         }
         atomicAdd(pc.totals + 0, e); // two pass contexts may tally at the same time
         atomicAdd(pc.totals + 1, s);

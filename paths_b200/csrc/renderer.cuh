@@ -4,7 +4,9 @@
 #pragma once
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
+#include <string>
 #include <vector>
 
 #include "pipeline.cuh"
@@ -74,6 +76,64 @@ template <typename R> __global__ void k_add_sums(typename Vec4T<R>::type *sums, 
     sums[i] = s;
 }
 
+// ------------------------------------------------------------------ which traversal kernels a scene runs on
+// ONE selection shared by RendererImpl (the render) and the per-ray seam (paths_trace_closest / paths_trace_occluded with precision
+// 32), so that a fixed-ray test drives exactly the kernels, node layout and grids a render of the same scene launches.
+struct TraceConfig {
+    int sm_count = 148;
+    int variant = 3;    // bounce and visibility rays: 0 plain batches (k_extend / k_shadow), 3 two-wide lane refill, 16 four-wide
+    int variant_b0 = 1; // camera segment: 1 = k_camera_extend (raygen fused with a plain-batch closest hit), 0/3/16 = k_raygen + that kernel
+    int grid_trace = 0, grid_camera = 0, grid4 = 0;
+    size_t smem4 = 0;
+};
+
+// stack overflows of the two-wide kernels (dev_trace.cuh) since the library was loaded, on the current device
+static inline paths_status read_stack_overflows(unsigned long long *out, std::string &err) {
+    PATHS_CU(cudaMemcpyFromSymbol(out, g_stack_overflows, sizeof(unsigned long long)));
+    return PATHS_OK;
+}
+
+template <typename R> paths_status configure_trace(const SceneDevice *sd, TraceConfig &tc, std::string &err) {
+    cudaDeviceProp prop;
+    PATHS_CU(cudaGetDeviceProperties(&prop, sd->device));
+    tc.sm_count = prop.multiProcessorCount;
+    // two-wide nodes + local stack for small (L1-resident) scenes, four-wide nodes + shared-memory stack above 64k primitives
+    // (measured: teapot 7.5 vs 7.8 ms, dragon 25.4 vs 24.4 ms per 16 spp; profiles/r01_*)
+    tc.variant = sd->view.n_prims > 65536u ? 16 : 3;
+    tc.variant_b0 = 1;
+#ifdef PATHS_DEV_SWITCHES /* development builds only (make EXTRA=-DPATHS_DEV_SWITCHES): a stale variable must not change a release run */
+    if (const char *v = getenv("PATHS_EXTEND_VARIANT")) {
+        int want = atoi(v);
+        if (want == 0 || want == 3 || want == 16) tc.variant = want;
+    }
+    if (const char *v = getenv("PATHS_EXTEND_B0")) tc.variant_b0 = atoi(v);
+#endif
+    int bps = 0;
+    if constexpr (IsF64<R>::value) {
+        PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (k_extend<R, false>), 128, 0));
+        tc.grid_trace = tc.sm_count * std::max(bps, 1);
+        tc.variant = 0;
+        tc.variant_b0 = 0;
+    } else {
+        PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (k_extend_refill<1, 16, 8>), 128, 0));
+        tc.grid_trace = tc.sm_count * std::max(bps, 1);
+        PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_camera_extend<float>, 128, 0));
+        tc.grid_camera = tc.sm_count * std::max(bps, 1);
+        // four-wide kernels: stack of 3 * depth + 1 levels per thread in shared memory
+        tc.smem4 = (size_t)(3 * sd->view.fast4_depth + 1) * 128 * sizeof(int32_t);
+        if (tc.smem4 > 200 * 1024 || !sd->view.fast4_nodes) {
+            if (tc.variant == 16) tc.variant = 3; // pathological tree: the two-wide kernels keep their stack in local memory
+            tc.smem4 = 0;
+        } else {
+            PATHS_CU(cudaFuncSetAttribute(k_shadow4<4, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc.smem4));
+            PATHS_CU(cudaFuncSetAttribute(k_extend4s<1, 16, 16, 12>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc.smem4));
+            PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_extend4s<1, 16, 16, 12>, 128, tc.smem4));
+            tc.grid4 = tc.sm_count * std::max(bps, 1);
+        }
+    }
+    return PATHS_OK;
+}
+
 // ------------------------------------------------------------------ batch queries
 template <typename R, bool MIXED>
 __global__ void k_trace_closest(DevScene sc, const double *o, const double *d, uint32_t n, uint32_t *prim, double *t, double *bary) {
@@ -115,37 +175,186 @@ __global__ void k_camera_rays(DevCamera cam, uint32_t k0, uint32_t k1, uint32_t 
     weight[i] = wt;
 }
 
+// ---- the per-ray seam over the PRODUCTION kernels: host rays are staged into a PathState exactly like the one a render pass keeps,
+// the kernels a render would launch for this scene (TraceConfig) run over it, and the hit / radiance records are read back.
+template <typename R4> __global__ void k_stage_rays(const double *o, const double *d, uint32_t n, R4 *ray_pairs) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    typedef decltype(ray_pairs->x) S;
+    ray_pairs[2 * i] = mk4(S(o[3 * i]), S(o[3 * i + 1]), S(o[3 * i + 2]), S(0));
+    ray_pairs[2 * i + 1] = mk4(S(d[3 * i]), S(d[3 * i + 1]), S(d[3 * i + 2]), S(0));
+}
+template <typename R4> __global__ void k_unstage_hits(const R4 *hit, DevScene sc, uint32_t n, uint32_t *prim, double *t, double *bary) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    typedef decltype(hit->x) S;
+    R4 h = hit[i];
+    uint32_t p = real_to_bits(h.x);
+    bool is_hit = p != 0xFFFFFFFFu;
+    prim[i] = p;
+    t[i] = is_hit ? (double)h.y : (double)__int_as_float(0x7f800000);
+    if (bary) {
+        bool tri = is_hit && (sc.prim_meta[p].x & PATHS_PM_TRI);
+        bary[3 * i] = tri ? (double)h.z : 0.0;
+        bary[3 * i + 1] = tri ? (double)h.w : 0.0;
+        bary[3 * i + 2] = tri ? (double)(S(1.0) - h.z - h.w) : 0.0;
+    }
+}
+// visibility records as k_shade writes them: origin | light, direction | slot, contribution; slot i's radiance record starts at zero
+template <typename R4> __global__ void k_stage_shadow(const double *o, const double *d, const uint32_t *light, uint32_t n, R4 *sh_o, R4 *sh_d, R4 *sh_c,
+                                                      R4 *col) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    typedef decltype(sh_o->x) S;
+    sh_o[i] = mk4(S(o[3 * i]), S(o[3 * i + 1]), S(o[3 * i + 2]), bits_to_real(light ? light[i] : PATHS_LIGHT_ENV, S(0)));
+    sh_d[i] = mk4(S(d[3 * i]), S(d[3 * i + 1]), S(d[3 * i + 2]), bits_to_real(i, S(0)));
+    sh_c[i] = mk4(S(1), S(2), S(4), S(0));
+    col[i] = mk4(S(0), S(0), S(0), S(0));
+}
+template <typename R4> __global__ void k_unstage_shadow(const R4 *col, uint32_t n, uint8_t *occluded) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    typedef decltype(col->x) S;
+    R4 c = col[i];
+    // an unoccluded record adds its contribution (1, 2, 4) to the slot exactly once; anything else is reported as code 2
+    occluded[i] = (c.x == S(0) && c.y == S(0) && c.z == S(0)) ? 1 : ((c.x == S(1) && c.y == S(2) && c.z == S(4)) ? 0 : 2);
+}
+
+struct DevScratch { // frees what a batch call allocated, whatever way it returns
+    std::vector<void *> ptrs;
+    ~DevScratch() {
+        for (void *p : ptrs) cudaFree(p);
+    }
+    template <typename T> cudaError_t get(T **p, size_t count) {
+        void *q = nullptr;
+        cudaError_t e = cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(T));
+        if (e == cudaSuccess) ptrs.push_back(q);
+        *p = (T *)q;
+        return e;
+    }
+};
+
+// kernel: 0 = the selection a render makes for bounce rays; PATHS_TRACE_CAMERA / _TWO_WIDE / _FOUR_WIDE / _PLAIN force one
 template <typename R, bool MIXED = false>
 paths_status trace_closest_impl(const SceneDevice *sd, const double *o, const double *d, size_t n, uint32_t *prim, double *t, double *bary,
-                                std::string &err) {
+                                int kernel, std::string &err) {
+    typedef typename Vec4T<R>::type R4;
     if (n == 0) return PATHS_OK;
-    if (n > 0x7FFFFFFFu) {
+    if (n > 0x3FFFFFFFu) {
         err = "too many rays in one batch";
         return PATHS_ERR_INVALID_ARG;
     }
     PATHS_CU(cudaSetDevice(sd->device));
+    DevScratch mem;
     double *d_o = nullptr, *d_d = nullptr, *d_t = nullptr, *d_b = nullptr;
-    uint32_t *d_p = nullptr;
-    paths_status st = PATHS_OK;
-    auto body = [&]() -> paths_status {
-        PATHS_CU(cudaMalloc(&d_o, n * 24));
-        PATHS_CU(cudaMalloc(&d_d, n * 24));
-        PATHS_CU(cudaMalloc(&d_t, n * 8));
-        PATHS_CU(cudaMalloc(&d_p, n * 4));
-        if (bary) PATHS_CU(cudaMalloc(&d_b, n * 24));
-        PATHS_CU(cudaMemcpy(d_o, o, n * 24, cudaMemcpyHostToDevice));
-        PATHS_CU(cudaMemcpy(d_d, d, n * 24, cudaMemcpyHostToDevice));
-        k_trace_closest<R, MIXED><<<(unsigned)((n + 127) / 128), 128>>>(sd->view, d_o, d_d, (uint32_t)n, d_p, d_t, d_b);
-        PATHS_CU(cudaGetLastError());
-        PATHS_CU(cudaDeviceSynchronize());
-        PATHS_CU(cudaMemcpy(prim, d_p, n * 4, cudaMemcpyDeviceToHost));
-        PATHS_CU(cudaMemcpy(t, d_t, n * 8, cudaMemcpyDeviceToHost));
-        if (bary) PATHS_CU(cudaMemcpy(bary, d_b, n * 24, cudaMemcpyDeviceToHost));
-        return PATHS_OK;
-    };
-    st = body();
-    cudaFree(d_o); cudaFree(d_d); cudaFree(d_t); cudaFree(d_p); cudaFree(d_b);
-    return st;
+    uint32_t *d_p = nullptr, *ctl = nullptr;
+    PATHS_CU(mem.get(&d_o, n * 3));
+    PATHS_CU(mem.get(&d_d, n * 3));
+    PATHS_CU(mem.get(&d_t, n));
+    PATHS_CU(mem.get(&d_p, n));
+    if (bary) PATHS_CU(mem.get(&d_b, n * 3));
+    PATHS_CU(cudaMemcpy(d_o, o, n * 24, cudaMemcpyHostToDevice));
+    PATHS_CU(cudaMemcpy(d_d, d, n * 24, cudaMemcpyHostToDevice));
+    const unsigned blocks = (unsigned)((n + 127) / 128);
+    bool staged = false;
+    if constexpr (!IsF64<R>::value) {
+        if (kernel != PATHS_TRACE_CAMERA) { // the bounce-ray kernels of a render pass, over a staged path state
+            TraceConfig tc;
+            paths_status st = configure_trace<R>(sd, tc, err);
+            if (st != PATHS_OK) return st;
+            int variant = kernel == PATHS_TRACE_TWO_WIDE ? 3 : kernel == PATHS_TRACE_FOUR_WIDE ? 16 : kernel == PATHS_TRACE_PLAIN ? 0 : tc.variant;
+            if (variant == 16 && tc.grid4 == 0) {
+                err = "the four-wide tree of this scene is not staged (or too deep for its shared-memory stack)";
+                return PATHS_ERR_UNSUPPORTED;
+            }
+            PathState<R4> ps;
+            std::memset(&ps, 0, sizeof(ps));
+            PATHS_CU(mem.get(&ps.ray_o, 2 * n));
+            ps.ray_d = ps.ray_o + 1;
+            PATHS_CU(mem.get(&ps.hit, n));
+            PATHS_CU(mem.get(&ctl, 2));
+            const uint32_t host_ctl[2] = {(uint32_t)n, 0u}; // queue length, fetch cursor
+            PATHS_CU(cudaMemcpy(ctl, host_ctl, sizeof(host_ctl), cudaMemcpyHostToDevice));
+            k_stage_rays<R4><<<blocks, 128>>>(d_o, d_d, (uint32_t)n, ps.ray_o);
+            if (variant == 16) k_extend4s<1, 16, 16, 12><<<tc.grid4, 128, tc.smem4>>>(sd->view, ps, nullptr, ctl, ctl + 1);
+            else if (variant == 3) k_extend_refill<1, 16, 8><<<tc.grid_trace, 128>>>(sd->view, ps, nullptr, ctl, ctl + 1);
+            else k_extend<R, false><<<tc.grid_trace, 128>>>(sd->view, ps, nullptr, ctl, ctl + 1);
+            k_unstage_hits<R4><<<blocks, 128>>>(ps.hit, sd->view, (uint32_t)n, d_p, d_t, d_b);
+            staged = true;
+        }
+    }
+    if (!staged) k_trace_closest<R, MIXED><<<blocks, 128>>>(sd->view, d_o, d_d, (uint32_t)n, d_p, d_t, d_b);
+    PATHS_CU(cudaGetLastError());
+    PATHS_CU(cudaDeviceSynchronize());
+    PATHS_CU(cudaMemcpy(prim, d_p, n * 4, cudaMemcpyDeviceToHost));
+    PATHS_CU(cudaMemcpy(t, d_t, n * 8, cudaMemcpyDeviceToHost));
+    if (bary) PATHS_CU(cudaMemcpy(bary, d_b, n * 24, cudaMemcpyDeviceToHost));
+    return PATHS_OK;
+}
+
+// The shadow query of trace.rs:61-66 over a batch of host rays, through the visibility kernel a render launches for this scene and
+// arithmetic type (k_shadow_refill / k_shadow4 in f32, k_shadow in f64 and mixed mode).  light[i] = index of the light the ray was
+// sampled toward (its own primitive does not occlude it), or null: nothing is exempt.  occluded[i]: 1 blocked, 0 clear.
+template <typename R, bool MIXED = false>
+paths_status trace_occluded_impl(const SceneDevice *sd, const double *o, const double *d, const uint32_t *light, size_t n, uint8_t *occluded,
+                                 int kernel, std::string &err) {
+    typedef typename Vec4T<R>::type R4;
+    if (n == 0) return PATHS_OK;
+    if (n > 0x3FFFFFFFu) {
+        err = "too many rays in one batch";
+        return PATHS_ERR_INVALID_ARG;
+    }
+    PATHS_CU(cudaSetDevice(sd->device));
+    TraceConfig tc;
+    paths_status st = configure_trace<R>(sd, tc, err);
+    if (st != PATHS_OK) return st;
+    int variant = kernel == PATHS_TRACE_TWO_WIDE ? 3 : kernel == PATHS_TRACE_FOUR_WIDE ? 16 : kernel == PATHS_TRACE_PLAIN ? 0 : tc.variant;
+    if (IsF64<R>::value) variant = 0;
+    if (variant == 16 && tc.grid4 == 0) {
+        err = "the four-wide tree of this scene is not staged (or too deep for its shared-memory stack)";
+        return PATHS_ERR_UNSUPPORTED;
+    }
+    DevScratch mem;
+    double *d_o = nullptr, *d_d = nullptr;
+    uint32_t *d_l = nullptr, *ctl = nullptr;
+    uint8_t *d_occ = nullptr;
+    unsigned long long *totals = nullptr;
+    PathState<R4> ps;
+    std::memset(&ps, 0, sizeof(ps));
+    PATHS_CU(mem.get(&d_o, n * 3));
+    PATHS_CU(mem.get(&d_d, n * 3));
+    if (light) PATHS_CU(mem.get(&d_l, n));
+    PATHS_CU(mem.get(&d_occ, n));
+    PATHS_CU(mem.get(&ps.sh_o, n));
+    PATHS_CU(mem.get(&ps.sh_d, n));
+    PATHS_CU(mem.get(&ps.sh_c, n));
+    PATHS_CU(mem.get(&ps.col, n));
+    PATHS_CU(mem.get(&ctl, 2));
+    PATHS_CU(mem.get(&totals, 4));
+    PATHS_CU(cudaMemset(totals, 0, 4 * sizeof(unsigned long long)));
+    const uint32_t host_ctl[2] = {(uint32_t)n, 0u};
+    PATHS_CU(cudaMemcpy(ctl, host_ctl, sizeof(host_ctl), cudaMemcpyHostToDevice));
+    PATHS_CU(cudaMemcpy(d_o, o, n * 24, cudaMemcpyHostToDevice));
+    PATHS_CU(cudaMemcpy(d_d, d, n * 24, cudaMemcpyHostToDevice));
+    if (light) PATHS_CU(cudaMemcpy(d_l, light, n * 4, cudaMemcpyHostToDevice));
+    const unsigned blocks = (unsigned)((n + 127) / 128);
+    k_stage_shadow<R4><<<blocks, 128>>>(d_o, d_d, d_l, (uint32_t)n, ps.sh_o, ps.sh_d, ps.sh_c, ps.col);
+    bool launched = false;
+    if constexpr (!IsF64<R>::value) {
+        if (variant == 16) {
+            k_shadow4<4, 16, 2><<<tc.grid4, 128, tc.smem4>>>(sd->view, ps, ctl, ctl + 1, totals);
+            launched = true;
+        } else if (variant == 3) {
+            k_shadow_refill<1, 16, 8><<<tc.grid_trace, 128>>>(sd->view, ps, ctl, ctl + 1, totals);
+            launched = true;
+        }
+    }
+    if (!launched) k_shadow<R, MIXED><<<tc.grid_trace, 128>>>(sd->view, ps, ctl, ctl + 1, totals);
+    k_unstage_shadow<R4><<<blocks, 128>>>(ps.col, (uint32_t)n, d_occ);
+    PATHS_CU(cudaGetLastError());
+    PATHS_CU(cudaDeviceSynchronize());
+    PATHS_CU(cudaMemcpy(occluded, d_occ, n, cudaMemcpyDeviceToHost));
+    return PATHS_OK;
 }
 
 template <typename R>

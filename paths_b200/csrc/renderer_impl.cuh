@@ -38,10 +38,8 @@ template <typename R> class RendererImpl : public RendererBase {
     size_t n_slots_max_ = 0;
     bool mixed_ = false;        // f64 instantiation over the production tree (PATHS_PRECISION_MIXED)
     uint32_t samples_done_ = 0; // global samples per pixel issued so far (all ranks together)
-    int sm_count_ = 148, grid_trace_ = 0, grid_shade_ = 0, grid_stream_ = 0, variant_ = 3, grid4_ = 0, shade_variant_ = 1;
-    size_t smem4_ = 0;
-    int variant_b0_ = 1; // camera segment: 1 = raygen fused with a plain-batch closest hit, 0/3/16 = k_raygen + that extend variant
-    int grid_camera_ = 0;
+    TraceConfig tc_; // which traversal kernels this scene runs on (shared with the per-ray seam, renderer.cuh)
+    int grid_shade_ = 0, grid_stream_ = 0, shade_variant_ = 1;
     // device buffers
     R4 *sums_ = nullptr;
     uint32_t *pixels_ = nullptr; // tile shard: local -> global pixel
@@ -156,9 +154,6 @@ template <typename R> class RendererImpl : public RendererBase {
 
     paths_status init() {
         PATHS_CU(cudaSetDevice(sd_->device));
-        cudaDeviceProp prop;
-        PATHS_CU(cudaGetDeviceProperties(&prop, sd_->device));
-        sm_count_ = prop.multiProcessorCount;
         PATHS_CU(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
         uint32_t world = std::max<uint32_t>(opts_.world, 1);
         if (opts_.rank >= world) {
@@ -191,12 +186,14 @@ template <typename R> class RendererImpl : public RendererBase {
         PATHS_CU(cudaMemsetAsync(sums_, 0, (size_t)npix_ * sizeof(R4), stream_));
         // pass contexts: the second one only when kernels are not timed one by one (overlap would blur per-kernel times)
         n_ctx_ = opts_.time_kernels ? 1 : 2;
-        if (const char *v = getenv("PATHS_PIPELINE")) n_ctx_ = opts_.time_kernels ? 1 : std::min(4, std::max(1, atoi(v))); // development switch
+#ifdef PATHS_DEV_SWITCHES
+        if (const char *v = getenv("PATHS_PIPELINE")) n_ctx_ = opts_.time_kernels ? 1 : std::min(4, std::max(1, atoi(v)));
+#endif
         unsigned long long *totals = nullptr;
         if (alloc(&totals, 4) != PATHS_OK) return PATHS_ERR_CUDA;
         PATHS_CU(cudaMemsetAsync(totals, 0, 4 * sizeof(unsigned long long), stream_));
         const uint32_t nb = opts_.max_bounces + 2;
-        n_ctl_ = 5 * nb;
+        n_ctl_ = (3 + PATHS_NWORK) * nb;
         for (int c = 0; c < n_ctx_; c++) {
             PassCtx &x = ctx_[c];
             std::memset(&x.ps, 0, sizeof(x.ps));
@@ -215,7 +212,8 @@ template <typename R> class RendererImpl : public RendererBase {
             if (alloc(&x.ctl, n_ctl_) != PATHS_OK) return PATHS_ERR_CUDA;
             x.pc.qcount = x.ctl;
             x.pc.scount = x.ctl + nb;
-            x.pc.work = x.ctl + 2 * nb;
+            x.pc.ecount = x.ctl + 2 * nb;
+            x.pc.work = x.ctl + 3 * nb;
             x.pc.totals = totals;
             if (c == 0) x.stream = stream_;
             else PATHS_CU(cudaStreamCreateWithFlags(&x.stream, cudaStreamNonBlocking));
@@ -224,74 +222,54 @@ template <typename R> class RendererImpl : public RendererBase {
         PATHS_CU(cudaEventCreateWithFlags(&fork_, cudaEventDisableTiming));
         PATHS_CU(cudaEventCreateWithFlags(&join_, cudaEventDisableTiming));
         use_ctx(0);
-        // traversal kernel: two-wide nodes + local stack for small (L1-resident) scenes, four-wide nodes + shared-memory stack
-        // above 64k primitives (measured: teapot 7.5 vs 7.8 ms, dragon 25.4 vs 24.4 ms per 16 spp; profiles/r01_*)
-        variant_ = sd_->view.n_prims > 65536u ? 16 : 3;
-        if (const char *v = getenv("PATHS_EXTEND_VARIANT")) { // development switch: 0 plain batches, 3 two-wide refill, 16 four-wide
-            int want = atoi(v);
-            if (want == 0 || want == 3 || want == 16) variant_ = want;
+        // ---- traversal kernels and persistent grids (every SM full): the selection the per-ray seam shares
+        {
+            paths_status st = configure_trace<R>(sd_, tc_, err);
+            if (st != PATHS_OK) return st;
         }
+#ifdef PATHS_DEV_SWITCHES
         if (const char *v = getenv("PATHS_SHADE_VARIANT")) shade_variant_ = atoi(v);
-        if (const char *v = getenv("PATHS_EXTEND_B0")) variant_b0_ = atoi(v);
-        // ---- persistent grids: every SM full
+#endif
         int bps = 0;
-        if constexpr (IsF64<R>::value) PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (k_extend<R, false>), 128, 0));
-        else PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (k_extend_refill<1, 16, 8>), 128, 0));
-        grid_trace_ = sm_count_ * std::max(bps, 1);
-        if constexpr (!IsF64<R>::value) {
-            PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_camera_extend<float>, 128, 0));
-            grid_camera_ = sm_count_ * std::max(bps, 1);
-        }
         {
             const bool lights = sd_->view.n_lights > 0, ext = opts_.extensions != 0;
             if (ext) PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (k_shade<R, true, true>), 128, 0));
             else if (lights) PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (k_shade<R, true, false>), 128, 0));
             else PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (k_shade<R, false, false>), 128, 0));
         }
-        grid_shade_ = sm_count_ * std::max(bps, 1);
-        grid_stream_ = sm_count_ * 8;
-        if constexpr (!IsF64<R>::value) {
-            // four-wide kernels: stack of 3 * depth + 1 levels per thread in shared memory
-            smem4_ = (size_t)(3 * sd_->view.fast4_depth + 1) * 128 * sizeof(int32_t);
-            if (smem4_ > 200 * 1024) {
-                if (variant_ == 16) variant_ = 3; // pathological tree: the two-wide kernels keep their stack in local memory
-            } else {
-                PATHS_CU(cudaFuncSetAttribute(k_shadow4<4, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
-                PATHS_CU(cudaFuncSetAttribute(k_extend4s<1, 16, 16, 12>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4_));
-                PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_extend4s<1, 16, 16, 12>, 128, smem4_));
-                grid4_ = sm_count_ * std::max(bps, 1);
-            }
-        }
+        grid_shade_ = tc_.sm_count * std::max(bps, 1);
+        grid_stream_ = tc_.sm_count * 8;
         return PATHS_OK;
     }
 
     void launch_extend(const uint32_t *q, uint32_t b) {
         if constexpr (!IsF64<R>::value) {
             const uint32_t *cnt = pc_.qcount + b;
-            uint32_t *cur = pc_.work + 3 * b;
-            int vsel = (b == 0 && variant_b0_ >= 0) ? variant_b0_ : variant_;
+            uint32_t *cur = pc_.work + PATHS_NWORK * b;
+            int vsel = (b == 0 && tc_.variant_b0 >= 0) ? tc_.variant_b0 : tc_.variant;
             switch (vsel) { // 0 = one batch of 32 rays per warp at a time (k_extend), kept as the plain baseline
-            case 3: k_extend_refill<1, 16, 8><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 16: k_extend4s<1, 16, 16, 12><<<grid4_, 128, smem4_, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 3: k_extend_refill<1, 16, 8><<<tc_.grid_trace, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 16: k_extend4s<1, 16, 16, 12><<<tc_.grid4, 128, tc_.smem4, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
             default: break;
             }
         }
-        if (mixed_) k_extend<R, true><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, pc_.qcount + b, pc_.work + 3 * b);
-        else k_extend<R, false><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, q, pc_.qcount + b, pc_.work + 3 * b);
+        if (mixed_) k_extend<R, true><<<tc_.grid_trace, 128, 0, cs_>>>(sd_->view, ps_, q, pc_.qcount + b, pc_.work + PATHS_NWORK * b);
+        else k_extend<R, false><<<tc_.grid_trace, 128, 0, cs_>>>(sd_->view, ps_, q, pc_.qcount + b, pc_.work + PATHS_NWORK * b);
     }
-    void launch_shadow(uint32_t b) {
+    // visibility of the records [0, *count) of `ps`'s shadow arrays; `cursor` is this launch's dynamic-fetch counter
+    void launch_shadow(const PathState<R4> &ps, const uint32_t *count, uint32_t *cursor) {
         if constexpr (!IsF64<R>::value) {
-if (variant_ == 16) {
-                k_shadow4<4, 16, 2><<<grid4_, 128, smem4_, cs_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
+            if (tc_.variant == 16) {
+                k_shadow4<4, 16, 2><<<tc_.grid4, 128, tc_.smem4, cs_>>>(sd_->view, ps, count, cursor, pc_.totals);
                 return;
             }
-            if (variant_ != 0) {
-                k_shadow_refill<1, 16, 8><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
+            if (tc_.variant != 0) {
+                k_shadow_refill<1, 16, 8><<<tc_.grid_trace, 128, 0, cs_>>>(sd_->view, ps, count, cursor, pc_.totals);
                 return;
             }
         }
-        if (mixed_) k_shadow<R, true><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
-        else k_shadow<R, false><<<grid_trace_, 128, 0, cs_>>>(sd_->view, ps_, pc_.scount + b, pc_.work + 3 * b + 2, pc_.totals);
+        if (mixed_) k_shadow<R, true><<<tc_.grid_trace, 128, 0, cs_>>>(sd_->view, ps, count, cursor, pc_.totals);
+        else k_shadow<R, false><<<tc_.grid_trace, 128, 0, cs_>>>(sd_->view, ps, count, cursor, pc_.totals);
     }
 
     paths_status run_pass(uint32_t s_base, uint32_t n_spp) { return run_pass_on(pixels_, n_local_, s_base, n_spp); }
@@ -308,7 +286,7 @@ if (variant_ == 16) {
         const uint32_t nb = opts_.max_bounces + 1; // segments per path (trace.rs:13-16)
         PATHS_CU(cudaMemsetAsync(ctl_block_, 0, n_ctl_ * sizeof(uint32_t), cs_));
         bool fused_camera = false;
-        if constexpr (!IsF64<R>::value) fused_camera = variant_b0_ == 1;
+        if constexpr (!IsF64<R>::value) fused_camera = tc_.variant_b0 == 1;
         if (!fused_camera) {
             tic(0);
             k_raygen<R><<<grid_stream_, 256, 0, cs_>>>(cam_, k0, k1, shard, s_base, n_slots, ps_, pc_);
@@ -319,16 +297,16 @@ if (variant_ == 16) {
             tic(1);
             if (b == 0 && fused_camera) {
                 if constexpr (!IsF64<R>::value)
-                    k_camera_extend<float><<<grid_camera_, 128, 0, cs_>>>(sd_->view, cam_, k0, k1, shard, s_base, n_slots, ps_, pc_, pc_.work);
+                    k_camera_extend<float><<<tc_.grid_camera, 128, 0, cs_>>>(sd_->view, cam_, k0, k1, shard, s_base, n_slots, ps_, pc_, pc_.work);
             } else launch_extend(q, b);
             toc();
             stats_.n_extend_launches++;
             tic(2);
             {
-                uint32_t *shade_cursor = shade_variant_ == 1 ? nullptr : pc_.work + 3 * b + 1;
+                uint32_t *shade_cursor = shade_variant_ == 1 ? nullptr : pc_.work + PATHS_NWORK * b + 1;
                 uint32_t *qn = pc_.queue[(b + 1) & 1];
                 // three instantiations: every extension compiled in (lights or not) / lights only / neither
-#define PATHS_SHADE_ARGS sd_->view, ps_, shard, s_base, k0, k1, opts_.max_bounces, opts_.extensions, q, qn, pc_.qcount + b, pc_.qcount + b + 1, pc_.scount + b, shade_cursor, pc_.totals
+#define PATHS_SHADE_ARGS sd_->view, ps_, shard, s_base, k0, k1, opts_.max_bounces, opts_.extensions, q, qn, pc_.qcount + b, pc_.qcount + b + 1, pc_.scount + b, pc_.ecount + b, (uint32_t)n_slots_max_, shade_cursor, pc_.totals
                 if (opts_.extensions != 0) {
                     if (sd_->view.n_lights > 0) k_shade<R, true, true><<<grid_shade_, 128, 0, cs_>>>(PATHS_SHADE_ARGS);
                     else k_shade<R, false, true><<<grid_shade_, 128, 0, cs_>>>(PATHS_SHADE_ARGS);
@@ -337,9 +315,22 @@ if (variant_ == 16) {
 #undef PATHS_SHADE_ARGS
             }
             toc();
-            if (sd_->view.n_lights > 0 || ((opts_.extensions & PATHS_EXT_ENV_NEE) && sd_->view.sky_type == 2)) {
+            if (sd_->view.n_lights > 0) {
                 tic(3);
-                launch_shadow(b);
+                launch_shadow(ps_, pc_.scount + b, pc_.work + PATHS_NWORK * b + 2);
+                toc();
+                stats_.n_shadow_launches++;
+            }
+            // environment NEE records (extension) live in the second half of the shadow arrays and are resolved by a launch of their
+            // own: a path may emit a light record AND an environment record at one bounce, and two records of one slot inside one
+            // launch would race on its radiance record (plain load-add-store).  Stream order makes the sum deterministic.
+            if ((opts_.extensions & PATHS_EXT_ENV_NEE) && sd_->view.sky_type == 2) {
+                PathState<R4> pe = ps_;
+                pe.sh_o += n_slots_max_;
+                pe.sh_d += n_slots_max_;
+                pe.sh_c += n_slots_max_;
+                tic(3);
+                launch_shadow(pe, pc_.ecount + b, pc_.work + PATHS_NWORK * b + 3);
                 toc();
                 stats_.n_shadow_launches++;
             }
@@ -478,6 +469,16 @@ if (variant_ == 16) {
         stats_.shadow_rays = t[1];
         stats_.bad_samples = t[2];
         stats_.samples = t[3];
+        {
+            unsigned long long ovf = 0;
+            paths_status so = read_stack_overflows(&ovf, err);
+            if (so != PATHS_OK) return so;
+            stats_.stack_overflows = ovf;
+        }
+        stats_.extend_kernel = tc_.variant;
+        stats_.camera_kernel = tc_.variant_b0;
+        stats_.shade_kernel = shade_variant_;
+        stats_.pass_contexts = n_ctx_;
         *st = stats_;
         return PATHS_OK;
     }

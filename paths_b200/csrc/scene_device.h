@@ -58,8 +58,17 @@ DevCamera make_dev_camera(const paths_camera &c); // CameraDescription::to_camer
 // one factory + two batch entry points per arithmetic type, instantiated in kernels_f32.cu / kernels_f64.cu
 RendererBase *make_renderer_f32(const SceneDevice *sd, const paths_camera &cam, const paths_render_opts &opts, std::string &err);
 RendererBase *make_renderer_f64(const SceneDevice *sd, const paths_camera &cam, const paths_render_opts &opts, std::string &err);
+// kernel: 0 = the bounce-ray kernel a render launches for this scene, or a PATHS_TRACE_* code
 paths_status trace_closest_f32(const SceneDevice *sd, const double *o, const double *d, size_t n, uint32_t *prim, double *t, double *bary,
-                               std::string &err);
+                               int kernel, std::string &err);
+paths_status trace_occluded_f32(const SceneDevice *sd, const double *o, const double *d, const uint32_t *light, size_t n, uint8_t *occluded,
+                                int kernel, std::string &err);
+paths_status trace_occluded_f64(const SceneDevice *sd, const double *o, const double *d, const uint32_t *light, size_t n, uint8_t *occluded,
+                                std::string &err);
+paths_status trace_occluded_mixed(const SceneDevice *sd, const double *o, const double *d, const uint32_t *light, size_t n, uint8_t *occluded,
+                                  std::string &err);
+paths_status stack_overflows_f32(int device, unsigned long long *out, std::string &err);
+paths_status stack_overflows_f64(int device, unsigned long long *out, std::string &err);
 paths_status trace_closest_f64(const SceneDevice *sd, const double *o, const double *d, size_t n, uint32_t *prim, double *t, double *bary,
                                std::string &err);
 paths_status trace_closest_mixed(const SceneDevice *sd, const double *o, const double *d, size_t n, uint32_t *prim, double *t, double *bary,
