@@ -31,7 +31,8 @@ typedef enum {
     PATHS_ERR_PARSE = 3,
     PATHS_ERR_CUDA = 4,
     PATHS_ERR_UNSUPPORTED = 5,
-    PATHS_ERR_INTERNAL = 6
+    PATHS_ERR_INTERNAL = 6,
+    PATHS_ERR_NCCL = 7
 } paths_status;
 
 #define PATHS_MISS 0xFFFFFFFFu
@@ -117,6 +118,7 @@ typedef struct {
 
 typedef struct paths_scene paths_scene;
 typedef struct paths_renderer paths_renderer;
+typedef struct paths_group paths_group; /* one renderer per GPU of this process, rendering shards of one frame */
 
 /* ------------------------------------------------------------------ options */
 
@@ -270,6 +272,42 @@ paths_status paths_renderer_get_stats(paths_renderer *r, paths_stats *st);
 paths_status paths_renderer_set_camera(paths_renderer *r, const double location[3], const double rot[9]);
 /* reset() (renderer.rs:122-128) */
 paths_status paths_renderer_reset(paths_renderer *r);
+
+/* ---- several GPUs, one frame.  In the reference the merge of partial results is part of Renderer itself
+ * (drain_result_queue -> Estimator::update_pixel, src/renderer.rs:93-105); here it is paths_renderer_combine: the partial estimators
+ * of all ranks of a frame are combined on `root` over NCCL (NVLink / NVSwitch), enqueued on the renderer's stream behind its passes.
+ *   sample shards (PATHS_SHARD_SAMPLES): ncclReduce(sum) of the {sum r, sum g, sum b, count} buffers -- equal to one GPU up to the
+ *     order of the f32 additions;
+ *   tile shards (PATHS_SHARD_TILES): ranks own disjoint 64x64 tiles, so each packs its pixels and ncclSend's them, the root receives all
+ *     of them in one NCCL group and scatters them -- bit-identical to one GPU, 1/world of the bytes of a full-frame reduce.
+ * After a combine the root's image / estimator reads (image_f32, image_rgb24, get_sums) show the combined frame until the next sample is
+ * rendered; each rank's own estimator is left untouched, so render -> combine -> render -> combine accumulates correctly.
+ * NCCL is bound at run time (the libnccl.so.2 already loaded into the process, else the one on the loader path): PATHS_ERR_NCCL if none.
+ *
+ * One process per GPU (MPI / torchrun style): rank 0 calls paths_comm_unique_id and hands the 128 bytes to every rank out of band; every
+ * rank then calls paths_renderer_attach_comm (collective: returns when all `world` ranks of paths_render_opts have joined). */
+#define PATHS_COMM_ID_BYTES 128
+paths_status paths_comm_unique_id(uint8_t id[PATHS_COMM_ID_BYTES]);
+paths_status paths_renderer_attach_comm(paths_renderer *r, const uint8_t id[PATHS_COMM_ID_BYTES]);
+paths_status paths_renderer_combine(paths_renderer *r, int32_t root);       /* blocking */
+paths_status paths_renderer_combine_async(paths_renderer *r, int32_t root); /* pair with paths_renderer_sync */
+/* One process, several GPUs: the library owns one renderer, stream and NCCL rank per device (ncclCommInitAll).  opts->device, rank and
+ * world are ignored (rank i renders on device_ids[i], world = n_devices); device_ids = NULL means devices 0 .. n_devices-1.
+ * paths_group_render advances the frame by spp samples per pixel in total (sample shards: spp / n each; tile shards: all spp on every
+ * rank's own tiles) and combines on device_ids[0]; the image calls return the combined frame. */
+paths_status paths_group_create(paths_scene *s, const paths_camera *cam, const paths_render_opts *opts, int32_t n_devices,
+                                const int32_t *device_ids, paths_group **out);
+paths_status paths_group_render(paths_group *g, uint32_t spp);
+paths_status paths_group_image_f32(paths_group *g, float *rgb /* W*H*3 */);
+paths_status paths_group_image_rgb24(paths_group *g, uint8_t *rgb /* W*H*3 */);
+paths_status paths_group_get_sums(paths_group *g, double *sums4 /* W*H*4 */);
+/* counters summed over the devices; ms_device = the slowest device's */
+paths_status paths_group_get_stats(paths_group *g, paths_stats *st);
+/* the renderer of rank i, borrowed (per-device stats, stream, estimator); do not destroy it */
+paths_status paths_group_renderer(paths_group *g, int32_t i, paths_renderer **out);
+paths_status paths_group_set_camera(paths_group *g, const double location[3], const double rot[9]);
+paths_status paths_group_reset(paths_group *g);
+void paths_group_destroy(paths_group *g);
 
 /* ---- the interactive front half of Renderer (src/renderer.rs:143-192), single GPU.
  * render_preview = request_preview (renderer.rs:152-164): one sample for every 6th pixel in x and y.  The image calls show a pixel

@@ -14,7 +14,7 @@ from . import _capi
 from ._capi import (TRACE_CAMERA, TRACE_FOUR_WIDE, TRACE_PLAIN, TRACE_TWO_WIDE, EXT_ENV_NEE, EXT_GGX, EXT_MICROFACET, EXT_MICROFACET_COSINE, EXT_NEE_ALL_LIGHTS, MISS, PRECISION_AUTO, PRECISION_F32, PRECISION_F64, PRECISION_MIXED, SHARD_SAMPLES, SHARD_TILES, Camera, PathsError,  # noqa: F401
                     RenderOpts, SceneInfo, Stats, build, check, lib)
 
-__all__ = ["Scene", "Renderer", "Image", "Camera", "PathsError", "build", "lib", "camera_rays", "device_count", "MISS"]
+__all__ = ["Scene", "Renderer", "RendererGroup", "comm_unique_id", "Image", "Camera", "PathsError", "build", "lib", "camera_rays", "device_count", "MISS"]
 
 
 def _p(a):
@@ -321,9 +321,96 @@ class Renderer:
     def load_checkpoint(self, path):
         check(lib().paths_renderer_load_checkpoint(self._h, str(path).encode()))
 
+    # -- several GPUs, one frame: the combine of partial results lives inside Renderer in the reference too (renderer.rs:93-105)
+    def attach_comm(self, unique_id):
+        """Joins this renderer's rank to the frame's NCCL communicator (collective over all `world` ranks).  unique_id: the 128 bytes
+        rank 0 got from comm_unique_id(), handed to every rank out of band."""
+        buf = (C.c_uint8 * _capi.COMM_ID_BYTES).from_buffer_copy(bytes(unique_id))
+        check(lib().paths_renderer_attach_comm(self._h, buf))
+
+    def combine(self, root=0, wait=True):
+        """Combines the ranks' partial estimators on `root` over NCCL (sample shards: reduce; tile shards: send / receive of owned tiles).
+        On the root, render() / render_rgb24() / sums() then show the combined frame until new samples are rendered."""
+        check((lib().paths_renderer_combine if wait else lib().paths_renderer_combine_async)(self._h, int(root)))
+
     def shutdown(self):
         if self._h:
             lib().paths_renderer_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.shutdown()
+        except Exception:
+            pass
+
+
+def comm_unique_id():
+    """ncclGetUniqueId as 128 bytes (rank 0 calls it and broadcasts the result)."""
+    buf = (C.c_uint8 * _capi.COMM_ID_BYTES)()
+    check(lib().paths_comm_unique_id(buf))
+    return bytes(buf)
+
+
+class RendererGroup:
+    """One frame rendered by several GPUs of this process: one renderer, stream and NCCL rank per device, owned by the library.
+    render_samples(spp) advances the frame by spp samples per pixel in total and combines on the first device."""
+
+    def __init__(self, camera, scene, devices, precision=PRECISION_AUTO, seed=1, shard_mode=SHARD_SAMPLES, max_bounces=10,
+                 samples_per_pass=0, extensions=0):
+        self._h = None
+        self.scene = scene
+        self.camera = camera if isinstance(camera, Camera) else camera_from_dict(camera)
+        devices = list(range(devices)) if isinstance(devices, int) else list(devices)
+        o = RenderOpts()
+        lib().paths_render_opts_default(C.byref(o))
+        o.precision, o.seed, o.shard_mode, o.max_bounces, o.samples_per_pass, o.extensions = precision, seed, shard_mode, max_bounces, samples_per_pass, extensions
+        ids = (C.c_int32 * len(devices))(*devices)
+        h = C.c_void_p()
+        check(lib().paths_group_create(scene._h, C.byref(self.camera), C.byref(o), len(devices), ids, C.byref(h)))
+        self._h = h
+        self.n_devices = len(devices)
+        self.width, self.height = self.camera.image_width, self.camera.image_height
+
+    def render_samples(self, spp):
+        check(lib().paths_group_render(self._h, int(spp)))
+
+    def render(self):
+        px = np.empty((self.height, self.width, 3), dtype=np.float32)
+        check(lib().paths_group_image_f32(self._h, _p(px)))
+        return Image(self.width, self.height, px)
+
+    def render_rgb24(self):
+        px = np.empty((self.height, self.width, 3), dtype=np.uint8)
+        check(lib().paths_group_image_rgb24(self._h, _p(px)))
+        return px
+
+    def sums(self):
+        s = np.empty((self.height, self.width, 4), dtype=np.float64)
+        check(lib().paths_group_get_sums(self._h, _p(s)))
+        return s
+
+    def stats(self, rank=None):
+        st = Stats()
+        if rank is None:
+            check(lib().paths_group_get_stats(self._h, C.byref(st)))
+        else:
+            r = C.c_void_p()
+            check(lib().paths_group_renderer(self._h, int(rank), C.byref(r)))
+            check(lib().paths_renderer_get_stats(r, C.byref(st)))
+        return st.as_dict()
+
+    def set_camera(self, location, orientation):
+        loc = np.ascontiguousarray(location, dtype=np.float64)
+        rot = np.ascontiguousarray(orientation, dtype=np.float64).reshape(9)
+        check(lib().paths_group_set_camera(self._h, _p(loc), _p(rot)))
+
+    def reset(self):
+        check(lib().paths_group_reset(self._h))
+
+    def shutdown(self):
+        if self._h:
+            lib().paths_group_destroy(self._h)
             self._h = None
 
     def __del__(self):

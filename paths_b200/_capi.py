@@ -12,7 +12,8 @@ from pathlib import Path
 _PKG = Path(__file__).resolve().parent
 LIB_PATH = _PKG / "lib" / "libpaths_b200.so"
 
-OK, ERR_INVALID_ARG, ERR_IO, ERR_PARSE, ERR_CUDA, ERR_UNSUPPORTED, ERR_INTERNAL = range(7)
+OK, ERR_INVALID_ARG, ERR_IO, ERR_PARSE, ERR_CUDA, ERR_UNSUPPORTED, ERR_INTERNAL, ERR_NCCL = range(8)
+COMM_ID_BYTES = 128
 MISS = 0xFFFFFFFF
 PRECISION_AUTO, PRECISION_F32, PRECISION_MIXED, PRECISION_F64 = 0, 32, 48, 64
 TRACE_CAMERA, TRACE_TWO_WIDE, TRACE_PLAIN, TRACE_FOUR_WIDE = 33, 34, 35, 36  # f32 kernels the per-ray seam can be pointed at
@@ -126,6 +127,20 @@ SIGNATURES = {
     "paths_renderer_render": (C.c_int, [VP, C.c_uint32]),
     "paths_renderer_render_async": (C.c_int, [VP, C.c_uint32]),
     "paths_renderer_sync": (C.c_int, [VP]),
+    "paths_renderer_combine": (C.c_int, [VP, C.c_int32]),
+    "paths_renderer_combine_async": (C.c_int, [VP, C.c_int32]),
+    "paths_renderer_attach_comm": (C.c_int, [VP, VP]),
+    "paths_comm_unique_id": (C.c_int, [VP]),
+    "paths_group_create": (C.c_int, [VP, C.POINTER(Camera), C.POINTER(RenderOpts), C.c_int32, C.POINTER(C.c_int32), C.POINTER(VP)]),
+    "paths_group_render": (C.c_int, [VP, C.c_uint32]),
+    "paths_group_image_f32": (C.c_int, [VP, VP]),
+    "paths_group_image_rgb24": (C.c_int, [VP, VP]),
+    "paths_group_get_sums": (C.c_int, [VP, VP]),
+    "paths_group_get_stats": (C.c_int, [VP, C.POINTER(Stats)]),
+    "paths_group_renderer": (C.c_int, [VP, C.c_int32, C.POINTER(VP)]),
+    "paths_group_set_camera": (C.c_int, [VP, VP, VP]),
+    "paths_group_reset": (C.c_int, [VP]),
+    "paths_group_destroy": (None, [VP]),
     "paths_renderer_image_f32": (C.c_int, [VP, VP]),
     "paths_renderer_image_rgb24": (C.c_int, [VP, VP]),
     "paths_renderer_get_sums": (C.c_int, [VP, VP]),

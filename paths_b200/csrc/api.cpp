@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <exception>
 #include <limits>
+#include <memory>
 #include <mutex>
 #include <new>
 #include <string>
@@ -14,6 +15,7 @@
 #include <cuda_runtime_api.h>
 
 #include "loaders.h"
+#include "nccl_dyn.h"
 #include "scene_device.h"
 
 using namespace paths;
@@ -58,7 +60,16 @@ struct paths_renderer {
     paths_scene *scene = nullptr;
     uint32_t w = 0, h = 0;
     uint64_t seed = 0;
+    uint32_t rank = 0, world = 1;
+    int32_t device = 0;
     ~paths_renderer() { delete impl; }
+};
+
+struct paths_group {
+    std::vector<paths_renderer *> r; // r[i] = rank i on device_ids[i]; r[0] is the combine root
+    ~paths_group() {
+        for (paths_renderer *x : r) delete x;
+    }
 };
 
 namespace {
@@ -627,10 +638,196 @@ paths_status paths_renderer_create(paths_scene *s, const paths_camera *cam, cons
     r->w = cam->image_width;
     r->h = cam->image_height;
     r->seed = opts.seed;
+    r->rank = opts.rank;
+    r->world = std::max<uint32_t>(opts.world, 1);
+    r->device = opts.device;
     *out = r;
     return PATHS_OK;
     PATHS_GUARD_END
 }
+
+// ------------------------------------------------------------------ frame combine over NCCL
+paths_status paths_comm_unique_id(uint8_t id[PATHS_COMM_ID_BYTES]) {
+    PATHS_GUARD_BEGIN
+    static_assert(PATHS_COMM_ID_BYTES == NCCL_UNIQUE_ID_BYTES, "ncclUniqueId size");
+    if (!id) return fail(PATHS_ERR_INVALID_ARG, "null id");
+    std::string err;
+    const NcclApi *api = nccl_api(err);
+    if (!api) return fail(PATHS_ERR_NCCL, err);
+    ncclUniqueId uid;
+    ncclResult_t rr = api->GetUniqueId(&uid);
+    if (rr != ncclSuccess) return fail(PATHS_ERR_NCCL, std::string("ncclGetUniqueId: ") + api->GetErrorString(rr));
+    std::memcpy(id, uid.internal, PATHS_COMM_ID_BYTES);
+    return PATHS_OK;
+    PATHS_GUARD_END
+}
+
+paths_status paths_renderer_attach_comm(paths_renderer *r, const uint8_t id[PATHS_COMM_ID_BYTES]) {
+    PATHS_GUARD_BEGIN
+    if (!r || !id) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    if (r->impl->has_comm()) return fail(PATHS_ERR_INVALID_ARG, "a communicator is already attached to this renderer");
+    if (r->world < 2) return PATHS_OK; // an unsharded renderer has nothing to combine
+    std::string err;
+    const NcclApi *api = nccl_api(err);
+    if (!api) return fail(PATHS_ERR_NCCL, err);
+    if (cudaSetDevice(r->device) != cudaSuccess) return fail(PATHS_ERR_CUDA, "cudaSetDevice failed");
+    ncclUniqueId uid;
+    std::memcpy(uid.internal, id, PATHS_COMM_ID_BYTES);
+    ncclComm_t comm = nullptr;
+    ncclResult_t rr = api->CommInitRank(&comm, (int)r->world, uid, (int)r->rank);
+    if (rr != ncclSuccess) return fail(PATHS_ERR_NCCL, std::string("ncclCommInitRank: ") + api->GetErrorString(rr));
+    paths_status st = r->impl->attach_comm(comm, true);
+    return st == PATHS_OK ? st : fail(st, r->impl->err);
+    PATHS_GUARD_END
+}
+
+paths_status paths_group_create(paths_scene *s, const paths_camera *cam, const paths_render_opts *opts_in, int32_t n_devices,
+                                const int32_t *device_ids, paths_group **out) {
+    PATHS_GUARD_BEGIN
+    if (!s || !cam || !out) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    *out = nullptr;
+    if (n_devices < 1 || n_devices > 64) return fail(PATHS_ERR_INVALID_ARG, "n_devices out of range");
+    paths_render_opts opts;
+    if (opts_in) opts = *opts_in;
+    else paths_render_opts_default(&opts);
+    std::vector<int> devs(n_devices);
+    for (int i = 0; i < n_devices; i++) {
+        devs[i] = device_ids ? device_ids[i] : i;
+        paths_status st = check_device(devs[i]);
+        if (st != PATHS_OK) return st;
+        for (int j = 0; j < i; j++)
+            if (devs[j] == devs[i]) return fail(PATHS_ERR_INVALID_ARG, "a device is listed twice");
+    }
+    std::unique_ptr<paths_group> g(new paths_group());
+    for (int i = 0; i < n_devices; i++) {
+        paths_render_opts o = opts;
+        o.device = devs[i];
+        o.rank = (uint32_t)i;
+        o.world = (uint32_t)n_devices;
+        paths_renderer *r = nullptr;
+        paths_status st = paths_renderer_create(s, cam, &o, &r);
+        if (st != PATHS_OK) return st;
+        g->r.push_back(r);
+    }
+    if (n_devices > 1) {
+        std::string err;
+        const NcclApi *api = nccl_api(err);
+        if (!api) return fail(PATHS_ERR_NCCL, err);
+        std::vector<ncclComm_t> comms(n_devices, nullptr);
+        ncclResult_t rr = api->CommInitAll(comms.data(), n_devices, devs.data());
+        if (rr != ncclSuccess) return fail(PATHS_ERR_NCCL, std::string("ncclCommInitAll: ") + api->GetErrorString(rr));
+        for (int i = 0; i < n_devices; i++) g->r[i]->impl->attach_comm(comms[i], true);
+    }
+    *out = g.release();
+    return PATHS_OK;
+    PATHS_GUARD_END
+}
+
+paths_status paths_group_render(paths_group *g, uint32_t spp) {
+    PATHS_GUARD_BEGIN
+    if (!g) return fail(PATHS_ERR_INVALID_ARG, "null group");
+    // one host thread drives every device: all launches are asynchronous, and the combine of all ranks is issued inside one NCCL
+    // group, the documented pattern for several communicators in one thread
+    for (paths_renderer *r : g->r) {
+        paths_status st = r->impl->render(spp, false);
+        if (st != PATHS_OK) return fail(st, r->impl->err);
+    }
+    if (g->r.size() > 1) {
+        std::string err;
+        const NcclApi *api = nccl_api(err);
+        if (!api) return fail(PATHS_ERR_NCCL, err);
+        api->GroupStart();
+        paths_status bad = PATHS_OK;
+        std::string why;
+        for (paths_renderer *r : g->r) {
+            paths_status st = r->impl->combine(0, false);
+            if (st != PATHS_OK && bad == PATHS_OK) {
+                bad = st;
+                why = r->impl->err;
+            }
+        }
+        ncclResult_t rr = api->GroupEnd();
+        if (bad != PATHS_OK) return fail(bad, why);
+        if (rr != ncclSuccess) return fail(PATHS_ERR_NCCL, std::string("ncclGroupEnd: ") + api->GetErrorString(rr));
+    }
+    for (paths_renderer *r : g->r) {
+        paths_status st = r->impl->sync();
+        if (st != PATHS_OK) return fail(st, r->impl->err);
+    }
+    return PATHS_OK;
+    PATHS_GUARD_END
+}
+
+#define PATHS_GROUP_ROOT(expr)                                            \
+    PATHS_GUARD_BEGIN                                                     \
+    if (!g) return fail(PATHS_ERR_INVALID_ARG, "null group");             \
+    paths_renderer *r = g->r[0];                                          \
+    paths_status st = (expr);                                             \
+    return st == PATHS_OK ? st : fail(st, r->impl->err);                  \
+    PATHS_GUARD_END
+
+paths_status paths_group_image_f32(paths_group *g, float *rgb) {
+    if (!rgb) return fail(PATHS_ERR_INVALID_ARG, "null buffer");
+    PATHS_GROUP_ROOT(r->impl->image_f32(rgb))
+}
+paths_status paths_group_image_rgb24(paths_group *g, uint8_t *rgb) {
+    if (!rgb) return fail(PATHS_ERR_INVALID_ARG, "null buffer");
+    PATHS_GROUP_ROOT(r->impl->image_rgb24(rgb))
+}
+paths_status paths_group_get_sums(paths_group *g, double *sums4) {
+    if (!sums4) return fail(PATHS_ERR_INVALID_ARG, "null buffer");
+    PATHS_GROUP_ROOT(r->impl->get_sums(sums4))
+}
+paths_status paths_group_get_stats(paths_group *g, paths_stats *out) {
+    PATHS_GUARD_BEGIN
+    if (!g || !out) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    paths_stats tot;
+    std::memset(&tot, 0, sizeof(tot));
+    for (size_t i = 0; i < g->r.size(); i++) {
+        paths_stats st;
+        paths_status rc = g->r[i]->impl->get_stats(&st);
+        if (rc != PATHS_OK) return fail(rc, g->r[i]->impl->err);
+        if (i == 0) tot = st;
+        else {
+            tot.samples += st.samples; tot.extend_rays += st.extend_rays; tot.shadow_rays += st.shadow_rays; tot.bad_samples += st.bad_samples;
+            tot.kernel_launches += st.kernel_launches; tot.passes += st.passes; tot.stack_overflows += st.stack_overflows;
+            tot.n_extend_launches += st.n_extend_launches; tot.n_shadow_launches += st.n_shadow_launches;
+            tot.ms_raygen += st.ms_raygen; tot.ms_extend += st.ms_extend; tot.ms_shade += st.ms_shade; tot.ms_shadow += st.ms_shadow;
+            tot.ms_accumulate += st.ms_accumulate; tot.ms_total += st.ms_total;
+            tot.ms_device = std::max(tot.ms_device, st.ms_device);
+        }
+    }
+    *out = tot;
+    return PATHS_OK;
+    PATHS_GUARD_END
+}
+paths_status paths_group_renderer(paths_group *g, int32_t i, paths_renderer **out) {
+    if (!g || !out) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    if (i < 0 || (size_t)i >= g->r.size()) return fail(PATHS_ERR_INVALID_ARG, "rank out of range");
+    *out = g->r[i];
+    return PATHS_OK;
+}
+paths_status paths_group_set_camera(paths_group *g, const double location[3], const double rot[9]) {
+    PATHS_GUARD_BEGIN
+    if (!g || !location || !rot) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    for (paths_renderer *r : g->r) {
+        paths_status st = r->impl->set_camera(location, rot);
+        if (st != PATHS_OK) return fail(st, r->impl->err);
+    }
+    return PATHS_OK;
+    PATHS_GUARD_END
+}
+paths_status paths_group_reset(paths_group *g) {
+    PATHS_GUARD_BEGIN
+    if (!g) return fail(PATHS_ERR_INVALID_ARG, "null group");
+    for (paths_renderer *r : g->r) {
+        paths_status st = r->impl->reset();
+        if (st != PATHS_OK) return fail(st, r->impl->err);
+    }
+    return PATHS_OK;
+    PATHS_GUARD_END
+}
+void paths_group_destroy(paths_group *g) { delete g; }
 
 #define PATHS_FORWARD(expr)                                         \
     PATHS_GUARD_BEGIN                                               \
@@ -642,6 +839,8 @@ paths_status paths_renderer_create(paths_scene *s, const paths_camera *cam, cons
 paths_status paths_renderer_render(paths_renderer *r, uint32_t spp) { PATHS_FORWARD(r->impl->render(spp, true)) }
 paths_status paths_renderer_render_async(paths_renderer *r, uint32_t spp) { PATHS_FORWARD(r->impl->render(spp, false)) }
 paths_status paths_renderer_sync(paths_renderer *r) { PATHS_FORWARD(r->impl->sync()) }
+paths_status paths_renderer_combine(paths_renderer *r, int32_t root) { PATHS_FORWARD(r->impl->combine(root, true)) }
+paths_status paths_renderer_combine_async(paths_renderer *r, int32_t root) { PATHS_FORWARD(r->impl->combine(root, false)) }
 paths_status paths_renderer_image_f32(paths_renderer *r, float *rgb) {
     if (!rgb) return fail(PATHS_ERR_INVALID_ARG, "null buffer");
     PATHS_FORWARD(r->impl->image_f32(rgb))

@@ -9,6 +9,7 @@
 #include <string>
 #include <vector>
 
+#include "nccl_dyn.h"
 #include "pipeline.cuh"
 #include "scene_device.h"
 
@@ -132,6 +133,16 @@ template <typename R> paths_status configure_trace(const SceneDevice *sd, TraceC
         }
     }
     return PATHS_OK;
+}
+
+// ------------------------------------------------------------------ tile-shard combine: owned pixels <-> dense send buffers
+template <typename R4> __global__ void k_pack_pixels(const R4 *sums, const uint32_t *pixels, uint32_t n, R4 *out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = sums[pixels[i]];
+}
+template <typename R4> __global__ void k_scatter_pixels(const R4 *in, const uint32_t *pixels, uint32_t n, R4 *frame) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) frame[pixels[i]] = in[i];
 }
 
 // ------------------------------------------------------------------ batch queries

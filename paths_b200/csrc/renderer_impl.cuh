@@ -42,6 +42,16 @@ template <typename R> class RendererImpl : public RendererBase {
     int grid_shade_ = 0, grid_stream_ = 0, shade_variant_ = 1;
     // device buffers
     R4 *sums_ = nullptr;
+    // frame combine (NCCL): the communicator of this rank, the combined estimator on the root, tile-shard staging
+    ncclComm_t comm_ = nullptr;
+    bool comm_owned_ = false;
+    R4 *frame_ = nullptr;        // [npix_] combined estimator, allocated on the first combine this rank is the root of
+    bool frame_valid_ = false;   // the image / estimator reads show frame_ (set by combine on the root, cleared by any new sample)
+    R4 *pack_ = nullptr;         // tile shards: this rank's owned pixels, dense (send side) / every other rank's (root side)
+    size_t pack_elems_ = 0;
+    uint32_t *peer_pixels_ = nullptr; // root, tile shards: pixel lists of the other ranks, concatenated in rank order
+    int peer_pixels_root_ = -1;
+    std::vector<uint32_t> peer_counts_;
     uint32_t *pixels_ = nullptr; // tile shard: local -> global pixel
     // interactive front half (renderer.rs:143-192): column sweeps from the centre outwards, preview grid
     uint32_t *sweep_pixels_ = nullptr; // scratch local -> global table for column / preview passes [npix_]
@@ -138,6 +148,10 @@ template <typename R> class RendererImpl : public RendererBase {
             cudaEventDestroy(sp.second);
         }
         for (cudaEvent_t e : pool_) cudaEventDestroy(e);
+        if (comm_ && comm_owned_) {
+            std::string e;
+            if (const NcclApi *api = nccl_api(e)) api->CommDestroy(comm_);
+        }
         for (void *p : allocs_) cudaFree(p);
         if (stage_) cudaFree(stage_);
         for (int c = 1; c < 4; c++)
@@ -278,6 +292,7 @@ template <typename R> class RendererImpl : public RendererBase {
     paths_status run_pass_on(const uint32_t *pixels, uint32_t n_local, uint32_t s_base, uint32_t n_spp) {
         const uint32_t n_slots = n_local * n_spp;
         if (n_slots == 0) return PATHS_OK;
+        frame_valid_ = false;
         const uint32_t k0 = (uint32_t)opts_.seed, k1 = (uint32_t)(opts_.seed >> 32);
         ShardInfo shard;
         shard.n_local = n_local;
@@ -417,7 +432,7 @@ template <typename R> class RendererImpl : public RendererBase {
         PATHS_CU(cudaSetDevice(sd_->device));
         float *d = nullptr;
         if (staging((size_t)npix_ * 12, (void **)&d) != PATHS_OK) return PATHS_ERR_CUDA;
-        k_image_f32<R><<<(npix_ + 255) / 256, 256, 0, stream_>>>(sums_, npix_, W_, d);
+        k_image_f32<R><<<(npix_ + 255) / 256, 256, 0, stream_>>>(shown(), npix_, W_, d);
         PATHS_CU(cudaMemcpyAsync(rgb, d, (size_t)npix_ * 12, cudaMemcpyDeviceToHost, stream_));
         PATHS_CU(cudaStreamSynchronize(stream_));
         return PATHS_OK;
@@ -426,7 +441,7 @@ template <typename R> class RendererImpl : public RendererBase {
         PATHS_CU(cudaSetDevice(sd_->device));
         uint8_t *d = nullptr;
         if (staging((size_t)npix_ * 3, (void **)&d) != PATHS_OK) return PATHS_ERR_CUDA;
-        k_image_rgb24<R><<<(npix_ + 255) / 256, 256, 0, stream_>>>(sums_, npix_, W_, d);
+        k_image_rgb24<R><<<(npix_ + 255) / 256, 256, 0, stream_>>>(shown(), npix_, W_, d);
         PATHS_CU(cudaMemcpyAsync(rgb, d, (size_t)npix_ * 3, cudaMemcpyDeviceToHost, stream_));
         PATHS_CU(cudaStreamSynchronize(stream_));
         return PATHS_OK;
@@ -435,7 +450,7 @@ template <typename R> class RendererImpl : public RendererBase {
         PATHS_CU(cudaSetDevice(sd_->device));
         double4 *d = nullptr;
         if (staging((size_t)npix_ * 32, (void **)&d) != PATHS_OK) return PATHS_ERR_CUDA;
-        k_sums_to_f64<R><<<(npix_ + 255) / 256, 256, 0, stream_>>>(sums_, npix_, d);
+        k_sums_to_f64<R><<<(npix_ + 255) / 256, 256, 0, stream_>>>(shown(), npix_, d);
         PATHS_CU(cudaMemcpyAsync(sums4, d, (size_t)npix_ * 32, cudaMemcpyDeviceToHost, stream_));
         PATHS_CU(cudaStreamSynchronize(stream_));
         return PATHS_OK;
@@ -444,11 +459,112 @@ template <typename R> class RendererImpl : public RendererBase {
         PATHS_CU(cudaSetDevice(sd_->device));
         double4 *d = nullptr;
         if (staging((size_t)npix_ * 32, (void **)&d) != PATHS_OK) return PATHS_ERR_CUDA;
+        frame_valid_ = false;
         PATHS_CU(cudaMemcpyAsync(d, sums4, (size_t)npix_ * 32, cudaMemcpyHostToDevice, stream_));
         k_add_sums<R><<<(npix_ + 255) / 256, 256, 0, stream_>>>(sums_, npix_, d);
         PATHS_CU(cudaStreamSynchronize(stream_));
         return PATHS_OK;
     }
+    // what Renderer::render shows: the combined frame right after a combine on its root, this rank's own estimator otherwise
+    const R4 *shown() const { return frame_valid_ ? frame_ : sums_; }
+
+    // ---- frame combine ----------------------------------------------------------------------------------------------------
+    bool has_comm() const override { return comm_ != nullptr; }
+    paths_status attach_comm(void *comm, bool owned) override {
+        if (comm_) {
+            err = "a communicator is already attached to this renderer";
+            return PATHS_ERR_INVALID_ARG;
+        }
+        comm_ = (ncclComm_t)comm;
+        comm_owned_ = owned;
+        return PATHS_OK;
+    }
+    static void owned_pixels(uint32_t W, uint32_t H, uint32_t rank, uint32_t world, std::vector<uint32_t> &own) {
+        own.clear();
+        uint32_t tiles_x = (W + 63) / 64;
+        for (uint32_t y = 0; y < H; y++)
+            for (uint32_t x = 0; x < W; x++)
+                if (((y / 64) * tiles_x + (x / 64)) % world == rank) own.push_back(x + y * W);
+    }
+    // Renderer::drain_result_queue -> Estimator::update_pixel (renderer.rs:93-105) across GPUs: partial estimators of all ranks are
+    // combined on `root`, enqueued on the renderer's stream behind its passes.  Sample shards: ncclReduce(sum) of the {sum r, g, b, n}
+    // buffers.  Tile shards: every rank owns disjoint pixels, so the owners' values are MOVED, not added: each rank packs its pixels into
+    // a dense buffer and sends it, the root receives the others' buffers in one NCCL group and scatters them -- bit-identical to one GPU
+    // and 1/world of the bytes a reduce of full frames moves.
+    paths_status combine(int32_t root, bool wait) override {
+        const uint32_t world = std::max<uint32_t>(opts_.world, 1);
+        if (world == 1) return wait ? sync() : PATHS_OK; // nothing to combine: the estimator is the frame
+        if (!comm_) {
+            err = "no communicator attached: call paths_renderer_attach_comm (or render through a paths_group)";
+            return PATHS_ERR_INVALID_ARG;
+        }
+        if (root < 0 || (uint32_t)root >= world) {
+            err = "combine root out of range";
+            return PATHS_ERR_INVALID_ARG;
+        }
+        std::string e;
+        const NcclApi *api = nccl_api(e);
+        if (!api) {
+            err = e;
+            return PATHS_ERR_NCCL;
+        }
+        PATHS_CU(cudaSetDevice(sd_->device));
+        const bool is_root = (uint32_t)root == opts_.rank;
+        const ncclDataType_t dt = IsF64<R>::value ? ncclDouble : ncclFloat;
+        if (is_root && !frame_ && alloc(&frame_, npix_) != PATHS_OK) return PATHS_ERR_CUDA;
+        if (opts_.shard_mode == PATHS_SHARD_SAMPLES) {
+            PATHS_NCCL(api, Reduce(sums_, is_root ? frame_ : nullptr, (size_t)npix_ * 4, dt, ncclSum, root, comm_, stream_));
+        } else if (!is_root) {
+            if (pack_elems_ < n_local_) {
+                if (alloc(&pack_, n_local_) != PATHS_OK) return PATHS_ERR_CUDA;
+                pack_elems_ = n_local_;
+            }
+            if (n_local_ > 0) {
+                k_pack_pixels<R4><<<(n_local_ + 255) / 256, 256, 0, stream_>>>(sums_, pixels_, n_local_, pack_);
+                PATHS_NCCL(api, Send(pack_, (size_t)n_local_ * 4, dt, root, comm_, stream_));
+            }
+        } else {
+            if (peer_pixels_root_ != root) { // the other ranks' pixel lists follow from the tile dealing: no exchange needed
+                std::vector<uint32_t> all, own;
+                peer_counts_.assign(world, 0);
+                for (uint32_t r = 0; r < world; r++) {
+                    if (r == opts_.rank) continue;
+                    owned_pixels(W_, H_, r, world, own);
+                    peer_counts_[r] = (uint32_t)own.size();
+                    all.insert(all.end(), own.begin(), own.end());
+                }
+                if (alloc(&peer_pixels_, all.size()) != PATHS_OK) return PATHS_ERR_CUDA;
+                if (!all.empty()) PATHS_CU(cudaMemcpy(peer_pixels_, all.data(), all.size() * 4, cudaMemcpyHostToDevice));
+                if (pack_elems_ < all.size()) {
+                    if (alloc(&pack_, all.size()) != PATHS_OK) return PATHS_ERR_CUDA;
+                    pack_elems_ = all.size();
+                }
+                peer_pixels_root_ = root;
+            }
+            // own pixels (and zeros elsewhere) first, then the others' pixels over them
+            PATHS_CU(cudaMemcpyAsync(frame_, sums_, (size_t)npix_ * sizeof(R4), cudaMemcpyDeviceToDevice, stream_));
+            size_t off = 0, total = 0;
+            PATHS_NCCL(api, GroupStart());
+            for (uint32_t r = 0; r < world; r++) {
+                if (r == opts_.rank || peer_counts_[r] == 0) continue;
+                ncclResult_t rr = api->Recv(pack_ + off, (size_t)peer_counts_[r] * 4, dt, (int)r, comm_, stream_);
+                if (rr != ncclSuccess) {
+                    api->GroupEnd();
+                    err = std::string("ncclRecv: ") + api->GetErrorString(rr);
+                    return PATHS_ERR_NCCL;
+                }
+                off += peer_counts_[r];
+            }
+            PATHS_NCCL(api, GroupEnd());
+            total = off;
+            if (total > 0) k_scatter_pixels<R4><<<(unsigned)((total + 255) / 256), 256, 0, stream_>>>(pack_, peer_pixels_, (uint32_t)total, frame_);
+        }
+        PATHS_CU(cudaGetLastError());
+        frame_valid_ = is_root;
+        stats_.kernel_launches += (opts_.shard_mode == PATHS_SHARD_TILES) ? 1 : 0;
+        return wait ? sync() : PATHS_OK;
+    }
+
     paths_status device_sums(void **ptr, size_t *n, int32_t *elem_bytes) override {
         *ptr = sums_;
         *n = (size_t)npix_ * 4;
@@ -495,6 +611,7 @@ template <typename R> class RendererImpl : public RendererBase {
         samples_done_ = 0;
         sweep_pos_ = 0;
         n_previews_ = 0;
+        frame_valid_ = false;
         resolve_timers();
         std::memset(&stats_, 0, sizeof(stats_));
         return PATHS_OK;

@@ -50,6 +50,11 @@ struct RendererBase {
     virtual paths_status render_columns(uint32_t n_requests) = 0;
     virtual paths_status get_progress(uint32_t *samples_done, uint32_t *sweep_pos) = 0;
     virtual paths_status set_progress(uint32_t samples_done) = 0;
+    // frame combine over NCCL (renderer.rs:93-105 is where the reference merges its workers' results): comm = ncclComm_t of this
+    // renderer's rank; owned = destroy it with the renderer
+    virtual paths_status attach_comm(void *comm, bool owned) = 0;
+    virtual paths_status combine(int32_t root, bool wait) = 0;
+    virtual bool has_comm() const = 0;
     std::string err;
 };
 
