@@ -111,8 +111,16 @@ def check_closest(pb, oracle_mod, case, gsc, rays, kernel, max_diff_frac):
     same = p0 == p1
     hit = same & (p0 != oracle_mod.MISS)
     assert hit.any()
-    rel = np.abs(t1[hit] - t0[hit]) / np.abs(t0[hit])
-    assert rel.max() <= 1e-4, f"{case.name}: t off by {rel.max():.3g} relative"
+    # t within 1e-4 relative (north_star).  A relative bound says nothing as t -> 0 (surface rays that dive back into the triangle
+    # they start on: t ~ 1e-8), so distances below the f32 resolution of the ray's own origin are held to that resolution instead:
+    # 16 ulp of the largest coordinate involved
+    err = np.abs(t1[hit] - t0[hit])
+    floor = 16 * 2.0**-23 * np.maximum(np.abs(o[hit]).max(axis=1), 1.0)
+    ok = (err <= 1e-4 * np.abs(t0[hit])) | (err <= floor)
+    worst = int(np.argmax(np.where(ok, 0.0, err)))
+    assert ok.all(), (f"{case.name} kernel {kernel}: {int((~ok).sum())} distances off, worst t0 {t0[hit][worst]!r} t1 {t1[hit][worst]!r} "
+                      f"origin {o[hit][worst]} prim {p0[hit][worst]}")
+    assert (err <= 1e-4 * np.abs(t0[hit])).mean() > 0.9999
     assert np.all(np.isinf(t1[same & ~hit]))
     n_diff = int((~same).sum())
     assert n_diff <= max_diff_frac * len(p0), f"{case.name}: {n_diff} of {len(p0)} ids differ"
