@@ -475,7 +475,9 @@ def run_ours(args, rank, world, local_rank):
             byt = sum(x["dram_bytes"] for x in pool)
             roof["traffic"] = byt / max(n_l, 1)
             scale = (n_samples / args.steps) / (1920 * 1080 * 16)  # the capture is one 16-spp pass; a step is this many of them
-            roof["dram_frac_measured"] = byt * scale / max(n_l, 1) / (dom_ms / n_dom_launch * 1e-3) / 1e9 / peak * (n_l / max(n_dom_launch / args.steps / scale, 1e-9)) if dom_ms > 0 else None
+            kernel_gbs = byt * scale / (dom_ms / args.steps * 1e-3) / 1e9 if dom_ms > 0 else None  # that class's DRAM bytes per step over its time per step
+            roof["dram_gbs_measured"] = kernel_gbs
+            roof["dram_frac_measured"] = kernel_gbs / peak if kernel_gbs is not None else None
             roof["dram_gbs_measured_step"] = sum(x["dram_bytes"] for x in c.values()) * scale / (rank_ms_step * 1e-3) / 1e9
             roof["dram_frac_measured_step"] = roof["dram_gbs_measured_step"] / peak
             roof["traffic_source"] = f"profiles/traffic.json[{args.scene}]: ncu dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel class, git head {tj['git_head']}, source hash {tj['source_hash']}"
@@ -507,7 +509,7 @@ def run_ours(args, rank, world, local_rank):
                     "what": f"set_camera (new epoch) + render + RGB24 frame to pinned host memory through the C ABI on {world} GPU(s)"
                             + (", combine on rank 0 inside the library (NCCL) inside the timed region" if world > 1 else "")},
             "gpu_launches": int(tot_launch),
-            "combine": None if world == 1 else ("paths_renderer_combine inside libpaths_b200.so: " + ("ncclSend/ncclRecv of owned 64x64 tiles" if args.shard == "tiles" else "ncclReduce(sum) of the float4 estimator") + f", NCCL from {pb.lib_nccl_origin()}"),
+            "combine": None if world == 1 else ("paths_renderer_combine inside libpaths_b200.so: " + ("ncclSend/ncclRecv of owned 64x64 tiles" if args.shard == "tiles" else "ncclReduce(sum) of the float4 estimator") + f", {pb.nccl_info()}"),
             "roofline": roof,
             "cpu_baseline": cpu,
             "cpu_baseline_t4": cpu_t4,

@@ -286,6 +286,8 @@ paths_status paths_renderer_reset(paths_renderer *r);
  *
  * One process per GPU (MPI / torchrun style): rank 0 calls paths_comm_unique_id and hands the 128 bytes to every rank out of band; every
  * rank then calls paths_renderer_attach_comm (collective: returns when all `world` ranks of paths_render_opts have joined). */
+/* "NCCL 2.28.9 from /path/libnccl.so.2" once bound, else why it cannot be */
+const char *paths_nccl_info(void);
 #define PATHS_COMM_ID_BYTES 128
 paths_status paths_comm_unique_id(uint8_t id[PATHS_COMM_ID_BYTES]);
 paths_status paths_renderer_attach_comm(paths_renderer *r, const uint8_t id[PATHS_COMM_ID_BYTES]);

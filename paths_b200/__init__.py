@@ -14,7 +14,7 @@ from . import _capi
 from ._capi import (TRACE_CAMERA, TRACE_FOUR_WIDE, TRACE_PLAIN, TRACE_TWO_WIDE, EXT_ENV_NEE, EXT_GGX, EXT_MICROFACET, EXT_MICROFACET_COSINE, EXT_NEE_ALL_LIGHTS, MISS, PRECISION_AUTO, PRECISION_F32, PRECISION_F64, PRECISION_MIXED, SHARD_SAMPLES, SHARD_TILES, Camera, PathsError,  # noqa: F401
                     RenderOpts, SceneInfo, Stats, build, check, lib)
 
-__all__ = ["Scene", "Renderer", "RendererGroup", "comm_unique_id", "Image", "Camera", "PathsError", "build", "lib", "camera_rays", "device_count", "MISS"]
+__all__ = ["Scene", "Renderer", "RendererGroup", "comm_unique_id", "nccl_info", "Image", "Camera", "PathsError", "build", "lib", "camera_rays", "device_count", "MISS"]
 
 
 def _p(a):
@@ -325,6 +325,7 @@ class Renderer:
     def attach_comm(self, unique_id):
         """Joins this renderer's rank to the frame's NCCL communicator (collective over all `world` ranks).  unique_id: the 128 bytes
         rank 0 got from comm_unique_id(), handed to every rank out of band."""
+        _preload_nccl()
         buf = (C.c_uint8 * _capi.COMM_ID_BYTES).from_buffer_copy(bytes(unique_id))
         check(lib().paths_renderer_attach_comm(self._h, buf))
 
@@ -345,8 +346,43 @@ class Renderer:
             pass
 
 
+_nccl_preloaded = False
+
+
+def _preload_nccl():
+    """The library binds whatever libnccl.so.2 the process already has.  In a Python process that may import PyTorch LATER, the copy
+    bound first must be the one PyTorch ships (an older system NCCL lacks symbols libtorch_cuda needs): map it before the first NCCL call."""
+    global _nccl_preloaded
+    if _nccl_preloaded:
+        return
+    _nccl_preloaded = True
+    import importlib.util
+    import os
+
+    try:
+        spec = importlib.util.find_spec("nvidia.nccl")
+    except (ImportError, ValueError):
+        spec = None
+    if spec and spec.submodule_search_locations:
+        for base in spec.submodule_search_locations:
+            path = os.path.join(base, "lib", "libnccl.so.2")
+            if os.path.exists(path):
+                try:
+                    C.CDLL(path, mode=C.RTLD_GLOBAL)
+                except OSError:
+                    pass
+                return
+
+
+def nccl_info():
+    """Which NCCL the library bound at run time (version and file), or why none could be."""
+    _preload_nccl()
+    return lib().paths_nccl_info().decode("utf-8", "replace")
+
+
 def comm_unique_id():
     """ncclGetUniqueId as 128 bytes (rank 0 calls it and broadcasts the result)."""
+    _preload_nccl()
     buf = (C.c_uint8 * _capi.COMM_ID_BYTES)()
     check(lib().paths_comm_unique_id(buf))
     return bytes(buf)
@@ -366,6 +402,8 @@ class RendererGroup:
         lib().paths_render_opts_default(C.byref(o))
         o.precision, o.seed, o.shard_mode, o.max_bounces, o.samples_per_pass, o.extensions = precision, seed, shard_mode, max_bounces, samples_per_pass, extensions
         ids = (C.c_int32 * len(devices))(*devices)
+        if len(devices) > 1:
+            _preload_nccl()
         h = C.c_void_p()
         check(lib().paths_group_create(scene._h, C.byref(self.camera), C.byref(o), len(devices), ids, C.byref(h)))
         self._h = h

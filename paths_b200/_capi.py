@@ -131,6 +131,7 @@ SIGNATURES = {
     "paths_renderer_combine_async": (C.c_int, [VP, C.c_int32]),
     "paths_renderer_attach_comm": (C.c_int, [VP, VP]),
     "paths_comm_unique_id": (C.c_int, [VP]),
+    "paths_nccl_info": (C.c_char_p, []),
     "paths_group_create": (C.c_int, [VP, C.POINTER(Camera), C.POINTER(RenderOpts), C.c_int32, C.POINTER(C.c_int32), C.POINTER(VP)]),
     "paths_group_render": (C.c_int, [VP, C.c_uint32]),
     "paths_group_image_f32": (C.c_int, [VP, VP]),

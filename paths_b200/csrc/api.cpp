@@ -647,6 +647,19 @@ paths_status paths_renderer_create(paths_scene *s, const paths_camera *cam, cons
 }
 
 // ------------------------------------------------------------------ frame combine over NCCL
+const char *paths_nccl_info(void) {
+    static thread_local std::string info;
+    std::string err;
+    const NcclApi *api = nccl_api(err);
+    if (!api) info = "NCCL unavailable: " + err;
+    else {
+        int v = 0;
+        api->GetVersion(&v);
+        info = "NCCL " + std::to_string(v / 10000) + "." + std::to_string(v / 100 % 100) + "." + std::to_string(v % 100) + " from " +
+               (api->origin.empty() ? std::string("the process image") : api->origin);
+    }
+    return info.c_str();
+}
 paths_status paths_comm_unique_id(uint8_t id[PATHS_COMM_ID_BYTES]) {
     PATHS_GUARD_BEGIN
     static_assert(PATHS_COMM_ID_BYTES == NCCL_UNIQUE_ID_BYTES, "ncclUniqueId size");

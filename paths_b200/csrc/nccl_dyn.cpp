@@ -4,6 +4,7 @@
 #include <dlfcn.h>
 #include <link.h>
 
+#include <cstdlib>
 #include <mutex>
 
 namespace paths {
@@ -31,6 +32,7 @@ const NcclApi *nccl_api(std::string &err) {
         g_tried = true;
         void *h = nullptr;
         const char *names[] = {"libnccl.so.2", "libnccl.so"};
+        if (const char *forced = getenv("PATHS_NCCL_LIB")) h = dlopen(forced, RTLD_NOW | RTLD_GLOBAL); // a deployment's own choice of file
         for (const char *n : names) // the copy the process already uses, if any
             if (!h) h = dlopen(n, RTLD_NOW | RTLD_NOLOAD);
         for (const char *n : names)

@@ -10,7 +10,12 @@ import pytest
 
 pytestmark = pytest.mark.gpu
 
-SCENES = ["spheres_on_plane", "bokeh_demo", "teapot", "bunny"]
+SCENES = ["spheres_on_plane", "bokeh_demo", "teapot", "bunny", "teapot_light"]
+
+
+def scene_path(name):
+    # reference scenes live under scenes/; test fixtures (e.g. the small vertex-coloured terrain) under tests/golden/
+    return f"tests/golden/{name[7:]}.yml" if name.startswith("golden:") else f"scenes/{name}.yml"
 
 
 @pytest.fixture(scope="module")
@@ -29,8 +34,8 @@ def scenes(pb, oracle_mod):
     def get(name, **kw):
         key = (name, tuple(sorted(kw.items())))
         if key not in cache:
-            osc, cam = oracle_mod.load_scene(f"scenes/{name}.yml", **kw)
-            gsc = pb.Scene.load(f"scenes/{name}.yml", width=kw.get("width", 0), height=kw.get("height", 0))
+            osc, cam = oracle_mod.load_scene(scene_path(name), **kw)
+            gsc = pb.Scene.load(scene_path(name), width=kw.get("width", 0), height=kw.get("height", 0))
             cache[key] = (osc, gsc, cam)
         return cache[key]
 
@@ -124,7 +129,8 @@ def _render_pair(pb, osc, gsc, cam, seed, spp, precision, **kw):
     return s, st, sums, counts, ctr
 
 
-@pytest.mark.parametrize("name,spp", [("spheres_on_plane", 4), ("bokeh_demo", 4), ("teapot", 3), ("bunny", 3)])
+@pytest.mark.parametrize("name,spp", [("spheres_on_plane", 4), ("bokeh_demo", 4), ("teapot", 3), ("bunny", 3), ("teapot_light", 3),
+                                      ("golden:vertex_colours", 3)])
 def test_image_f64_follows_oracle_sample_for_sample(pb, oracle_mod, scenes, name, spp):
     # trace.rs:7-121 end to end at a small resolution: same RNG streams, f64, reference tree => the estimator sums agree to
     # rounding in all but the rare pixels where a <= 2 ulp libm difference flips a discrete decision
@@ -138,7 +144,7 @@ def test_image_f64_follows_oracle_sample_for_sample(pb, oracle_mod, scenes, name
     assert abs(st["bad_samples"] - ctr.bad_samples) <= 2 + 2e-3 * ctr.bad_samples
 
 
-@pytest.mark.parametrize("name", ["teapot", "bunny", "spheres_on_plane"])
+@pytest.mark.parametrize("name", ["teapot", "bunny", "spheres_on_plane", "bokeh_demo", "teapot_light", "golden:vertex_colours"])
 def test_image_f32_within_monte_carlo_tolerance(pb, oracle_mod, scenes, name):
     # production kernels vs oracle at equal spp.  sigma0 = oracle(seed A) vs oracle(seed B) is the noise floor;
     # stated tolerance: relRMSE(GPU, oracle same seed) <= 0.5 * sigma0 (same streams => far below the floor) and
@@ -153,7 +159,14 @@ def test_image_f32_within_monte_carlo_tolerance(pb, oracle_mod, scenes, name):
     assert relrmse(g, b) <= 1.15 * sigma0 + 1e-6
     tol = 3.0 * sigma0 * a.mean(axis=(0, 1)) / np.sqrt(160 * 120) + 1e-6
     assert np.all(np.abs(g.mean(axis=(0, 1)) - a.mean(axis=(0, 1))) <= tol)
-    assert st["samples"] == 160 * 120 * spp
+    assert st["samples"] == 160 * 120 * spp and st["stack_overflows"] == 0
+    if name in ("teapot_light", "bunny", "golden:vertex_colours"):
+        assert st["shadow_rays"] > 0  # next-event estimation ran through the production visibility kernel
+    if name == "golden:vertex_colours":
+        # `albedo: {type: Vertex}` through the f32 tables: AUTO resolves to f32 (doom.yml, the reference's only vertex-coloured scene,
+        # resolves to mixed precision), and the image is visibly coloured by the mesh (channels differ pixel by pixel)
+        assert gsc.info["auto_precision"] == 32
+        assert np.abs(a[..., 0] - a[..., 2]).mean() > 0.01
 
 
 def test_tile_shards_are_bit_identical_to_one_gpu(pb, scenes):

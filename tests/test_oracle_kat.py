@@ -222,3 +222,182 @@ def test_flat_box_leaf_is_invisible(oracle_mod):
     sc = oracle_mod.Scene(desc)
     prim, t = sc.trace_closest(np.array([[0.25, 0.25, 0.0]]), np.array([[0.0, 0.0, 1.0]]))
     assert prim[0] == oracle_mod.MISS  # single leaf == root: root box test also fails
+
+
+# ----------------------------------------------------------------------------------------------------------------------------------
+# Closed-form checks.  The reference's tests pin nothing on intersection, materials, lights or the integrator, and the CUDA path is a
+# second restatement by the same hand, so GPU == oracle cannot catch a shared misreading.  The checks below derive the expected value
+# on paper from the reference's formulas (file:line in each) and compare the oracle with that -- evidence independent of the GPU code.
+
+
+def _mat(oracle_mod, d):
+    return oracle_mod.material_desc(d)
+
+
+def _sample(oracle_mod, m, vec_out, normal, u):
+    vo, n, uu = np.asarray(vec_out, dtype=np.float64), np.asarray(normal, dtype=np.float64), np.asarray(u, dtype=np.float64)
+    direction, brdf, pdf = np.zeros(3), np.zeros(3), C.c_double()
+    spec = oracle_mod.lib().orc_material_sample(C.byref(m), _p(vo), _p(n), _p(uu), _p(direction), C.byref(pdf), _p(brdf))
+    return direction, pdf.value, brdf, spec
+
+
+def test_closed_form_hemisphere_map_has_the_reference_quirk(oracle_mod):
+    # src/geom.rs:10-24: r = sqrt(u), theta = 2 pi v, local direction (r cos theta, 1 - u, r sin theta) -- y is 1 - u, not
+    # sqrt(1 - u), so the vector is not unit and not cosine-distributed.  After normalisation the polar cosine is
+    # (1 - u) / sqrt(u + (1 - u)^2) and the azimuth is theta.  With normal = +y and j.x == 0 the basis is i = x, k = i x j = +z
+    # (src/vector.rs:51-61), so world = local.
+    m = _mat(oracle_mod, {"type": "Lambertian", "albedo": {"type": "Rgb", "rgb": [0.2, 0.5, 0.9]}})
+    for u in (0.0, 0.1, 0.37, 0.5, 0.93, 0.999):
+        for v in (0.0, 0.125, 0.6, 0.99):
+            d, pdf, brdf, spec = _sample(oracle_mod, m, [0.0, 1.0, 0.0], [0.0, 1.0, 0.0], [0.3, u, v])
+            norm = math.sqrt(u + (1.0 - u) ** 2)
+            exp = np.array([math.sqrt(u) * math.cos(2 * math.pi * v), 1.0 - u, math.sqrt(u) * math.sin(2 * math.pi * v)]) / norm
+            assert np.allclose(d, exp, atol=1e-14) and not spec
+            # the CLAIMED density is the cosine lobe's (src/material.rs:220-222) and the brdf is albedo cos / pi (:237-239):
+            # the weight brdf / pdf is exactly the albedo, whatever the direction
+            assert abs(pdf - exp[1] / math.pi) < 1e-14
+            assert np.allclose(brdf / pdf, [0.2, 0.5, 0.9], rtol=1e-14)
+
+
+def test_closed_form_mirror_and_gloss_weights(oracle_mod):
+    n = np.array([0.0, 1.0, 0.0])
+    vo = np.array([0.6, 0.8, 0.0])  # cos(theta) = 0.8
+    # Mirror (src/material.rs:245-272): direction = 2 (n.v) n - v, pdf 1, brdf white, specular
+    d, pdf, brdf, spec = _sample(oracle_mod, _mat(oracle_mod, {"type": "Mirror"}), vo, n, [0.5, 0.5, 0.5])
+    assert np.allclose(d, [-0.6, 0.8, 0.0], atol=1e-15) and pdf == 1.0 and brdf.tolist() == [1.0, 1.0, 1.0] and spec
+    # Gloss (src/material.rs:302-325): r = r0 + (1 - r0)(1 - cos)^5; chance = r if r0 > 0.5 else 0.5; u0 <= chance -> mirror branch with
+    # weight (albedo metal + white (1 - metal)) r / chance, else Lambert branch with weight albedo (1 - metal)(1 - r) / (1 - chance)
+    alb, r0, metal = np.array([0.8, 0.3, 0.3]), 0.05, 0.25
+    m = _mat(oracle_mod, {"type": "Gloss", "albedo": {"type": "Rgb", "rgb": alb.tolist()}, "reflectance": r0, "metalness": metal})
+    r = r0 + (1.0 - r0) * 0.2**5
+    d, pdf, brdf, spec = _sample(oracle_mod, m, vo, n, [0.5, 0.3, 0.7])  # u0 = 0.5 <= chance = 0.5: specular
+    assert spec and np.allclose(d, [-0.6, 0.8, 0.0], atol=1e-15)
+    assert np.allclose(brdf / pdf, (alb * metal + (1.0 - metal)) * r / 0.5, rtol=1e-13)
+    d, pdf, brdf, spec = _sample(oracle_mod, m, vo, n, [0.500001, 0.3, 0.7])
+    assert not spec and np.allclose(brdf / pdf, alb * (1.0 - metal) * (1.0 - r) / 0.5, rtol=1e-13)
+    # white furnace: the expected weight over the branch choice is r (albedo metal + 1 - metal) + (1 - r)(1 - metal) albedo
+    us = (np.arange(4000) + 0.5) / 4000
+    acc = np.zeros(3)
+    for u0 in us:
+        _, pdf, brdf, _ = _sample(oracle_mod, m, vo, n, [u0, 0.3, 0.7])
+        acc += brdf / pdf
+    exp = r * (alb * metal + 1.0 - metal) + (1.0 - r) * (1.0 - metal) * alb
+    assert np.allclose(acc / len(us), exp, rtol=1e-12)
+    # a high-reflectance Gloss picks its mirror branch with probability r itself (r0 > 0.5)
+    m2 = _mat(oracle_mod, {"type": "Gloss", "albedo": {"type": "Rgb", "rgb": alb.tolist()}, "reflectance": 0.7, "metalness": 0.0})
+    r2 = 0.7 + 0.3 * 0.2**5
+    _, pdf, brdf, spec = _sample(oracle_mod, m2, vo, n, [r2 - 1e-9, 0.3, 0.7])
+    assert spec and np.allclose(brdf / pdf, [1.0, 1.0, 1.0], rtol=1e-13)
+    _, pdf, brdf, spec = _sample(oracle_mod, m2, vo, n, [r2 + 1e-9, 0.3, 0.7])
+    assert not spec and np.allclose(brdf / pdf, alb, rtol=1e-12)
+
+
+def test_closed_form_cook_torrance_brdf(oracle_mod):
+    # src/material.rs:436-447,503-523 at normal incidence and exit (v = l = n): h = n, alpha = 0, D = 1 / (pi m^2), G = min(1, 2, 2) = 1,
+    # brdf = albedo D G / (4 (n.v)(n.l)) = albedo / (4 pi m^2)
+    mdesc = _mat(oracle_mod, {"type": "CookTorrance", "albedo": {"type": "Rgb", "rgb": [0.9, 0.6, 0.3]}, "roughness": 0.4})
+    n = np.array([0.0, 1.0, 0.0])
+    out = np.zeros(3)
+    oracle_mod.lib().orc_material_brdf(C.byref(mdesc), _p(n), _p(-n), _p(n), _p(out))  # vec_in points INTO the surface
+    assert np.allclose(out, np.array([0.9, 0.6, 0.3]) / (4 * math.pi * 0.16), rtol=1e-12)
+    # 45 degrees in the plane of incidence, mirror configuration: h = n still, (n.v) = (n.l) = (v.h) = cos 45, G = min(1, 2 c c / c) = 1
+    c = math.sqrt(0.5)
+    vo, vi = np.array([c, c, 0.0]), np.array([c, -c, 0.0])
+    oracle_mod.lib().orc_material_brdf(C.byref(mdesc), _p(vo), _p(vi), _p(n), _p(out))
+    assert np.allclose(out, np.array([0.9, 0.6, 0.3]) / (math.pi * 0.16) / (4 * 0.5), rtol=1e-9)
+
+
+def test_closed_form_sphere_light_sample(oracle_mod):
+    # src/geom.rs:146-173: phi = acos(2 v - 1), theta = 2 pi u, n = (sin phi cos theta, sin phi sin theta, cos phi), point = c + r n,
+    # dir = (from - point) normalised, inv_pdf = max(0, 4 pi r^2 (n . dir) / |from - point|^2)
+    light = oracle_mod.light_desc({"geometry": "Sphere", "v": [0.0, 10.0, 0.0], "radius": 2.0, "colour": [1, 1, 1], "intensity": 1.0})
+    frm = np.array([0.0, 0.0, 0.0])
+    d, ip = np.zeros(3), C.c_double()
+    # v = 0 -> phi = pi -> n = (0, 0, -1): the point (0, 10, -2).  Seen from the origin it faces away: out = (0, -10, 2), n . dir < 0 -> 0
+    oracle_mod.lib().orc_light_sample(C.byref(light), _p(frm), 0.25, 0.0, _p(d), C.byref(ip))
+    assert np.allclose(d, np.array([0.0, -10.0, 2.0]) / math.sqrt(104.0), atol=1e-12) and ip.value == 0.0
+    # the same point seen from (3, 10, -6): out = (3, 0, -4), |out|^2 = 25, dir = (0.6, 0, -0.8), n . dir = 0.8 -> 16 pi 0.8 / 25
+    frm2 = np.array([3.0, 10.0, -6.0])
+    oracle_mod.lib().orc_light_sample(C.byref(light), _p(frm2), 0.25, 0.0, _p(d), C.byref(ip))
+    assert np.allclose(d, [0.6, 0.0, -0.8], atol=1e-12) and abs(ip.value - 16 * math.pi * 0.8 / 25.0) < 1e-12
+    # u = 0.25, v = 0.5 -> phi = pi/2, theta = pi/2 -> n = (0, 1, 0): the far pole (0, 12, 0), facing away: n . dir = -1 -> inv_pdf 0
+    oracle_mod.lib().orc_light_sample(C.byref(light), _p(frm), 0.25, 0.5, _p(d), C.byref(ip))
+    assert np.allclose(d, [0.0, -1.0, 0.0], atol=1e-12) and ip.value == 0.0
+    # u = 0.75 -> theta = 3 pi / 2 -> n = (0, -1, 0): the near pole (0, 8, 0): inv_pdf = 4 pi 4 / 64 = pi / 4
+    oracle_mod.lib().orc_light_sample(C.byref(light), _p(frm), 0.75, 0.5, _p(d), C.byref(ip))
+    assert np.allclose(d, [0.0, -1.0, 0.0], atol=1e-12) and abs(ip.value - math.pi / 4) < 1e-12
+    # Point lights hand back their vector as the direction with inv_pdf 1 (src/scene.rs:54-59)
+    pl = oracle_mod.light_desc({"geometry": "Point", "v": [0.3, -0.9, 0.1], "colour": [1, 1, 1], "intensity": 1.0})
+    oracle_mod.lib().orc_light_sample(C.byref(pl), _p(frm), 0.1, 0.2, _p(d), C.byref(ip))
+    assert d.tolist() == [0.3, -0.9, 0.1] and ip.value == 1.0
+
+
+def _furnace_scene(material, sky=(0.7, 0.7, 0.7)):
+    return {
+        "camera": {"image_width": 48, "image_height": 32, "location": [0.0, 0.0, -6.0], "pitch": 0.0, "yaw": 0.0, "roll": 0.0, "sensor_width": 0.036,
+                   "sensor_height": 0.024, "focal_length": 0.05, "focus_distance": 6.0, "aperture": 1e9},
+        "models": [],
+        "objects": [{"shape": "Sphere", "center": [0.0, 0.0, 0.0], "radius": 1.0, "material": material}],
+        "lights": [],
+        "sky": {"type": "Flat", "c0": list(sky), "c1": [0.0, 0.0, 0.0]},
+    }
+
+
+def test_closed_form_white_furnace(oracle_mod):
+    # trace.rs:7-121 end to end.  One convex Lambertian sphere under a flat sky of radiance c: the first hit's bounce always escapes (the
+    # sampled direction is in the upper hemisphere of a convex body), its weight brdf / pdf is exactly the albedo, and roulette does not
+    # start before the third segment -- so EVERY sample of a pixel on the sphere returns albedo * c times the camera weight
+    # (src/camera.rs:91: the z component of the normalised sensor-to-lens direction), and every other pixel returns c times it.
+    alb, sky = np.array([0.2, 0.5, 0.9]), np.array([0.7, 0.6, 0.5])
+    desc = _furnace_scene({"type": "Lambertian", "albedo": {"type": "Rgb", "rgb": alb.tolist()}}, sky)
+    sc, cam = oracle_mod.Scene(desc), desc["camera"]
+    spp = 6
+    sums, counts, ctr = sc.render(cam, 3, 0, spp)
+    assert counts.min() == spp and ctr.bad_samples == 0
+    ratios = []
+    for s in range(spp):
+        o, d, w = oracle_mod.camera_rays(cam, 3, s)
+        p, _ = sc.trace_closest(o, d)
+        hit = (p != oracle_mod.MISS).reshape(32, 48)
+        ratios.append((np.where(hit[..., None], alb * sky, sky)) * w.reshape(32, 48, 1))
+    assert np.allclose(sums, sum(ratios), rtol=1e-12, atol=1e-15)
+    # ... and a Mirror sphere reflects the flat sky unchanged: the whole image is c times the weight
+    descm = _furnace_scene({"type": "Mirror"}, sky)
+    scm = oracle_mod.Scene(descm)
+    sums_m, _, _ = scm.render(cam, 3, 0, 1)
+    o, d, w = oracle_mod.camera_rays(cam, 3, 0)
+    assert np.allclose(sums_m, sky * w.reshape(32, 48, 1), rtol=1e-12)
+    # Gloss sphere: E[weight] = r + (1 - r) albedo with r = Schlick(r0, cos) -- bounded by albedo <= E <= 1 per channel, and averaging
+    # many samples of the centre pixel (cos ~ 1, r ~ r0) gives r0 + (1 - r0) albedo within Monte Carlo error
+    r0 = 0.2
+    descg = _furnace_scene({"type": "Gloss", "albedo": {"type": "Rgb", "rgb": alb.tolist()}, "reflectance": r0, "metalness": 0.0}, (1.0, 1.0, 1.0))
+    descg["camera"]["image_width"], descg["camera"]["image_height"] = 3, 3
+    scg = oracle_mod.Scene(descg)
+    n = 4000
+    sums_g, _, _ = scg.render(descg["camera"], 5, 0, n)
+    _, _, wg = oracle_mod.camera_rays(descg["camera"], 5, 0)
+    centre = sums_g[1, 1] / n / wg.reshape(3, 3)[1, 1]
+    assert np.allclose(centre, r0 + (1.0 - r0) * alb, atol=0.02)
+
+
+def test_closed_form_sky_lookups(oracle_mod):
+    # src/scene.rs:88-113: gradient = overhead cos + horizon (1 - cos) with cos = dir . +y; HDRI is a nearest-texel equirect lookup:
+    # x = w/2 (atan2(z, x) / pi) + w/2, y = h (1 - acos(dir.y) / pi)
+    desc = _furnace_scene({"type": "Mirror"})
+    desc["sky"] = {"type": "Gradient", "c0": [0.5, 0.8, 0.9], "c1": [0.7, 0.85, 0.9]}
+    sc = oracle_mod.Scene(desc)
+    for dirv in ([0.0, 1.0, 0.0], [1.0, 0.0, 0.0], [0.6, 0.8, 0.0], [0.0, -1.0, 0.0]):
+        c = dirv[1]
+        assert np.allclose(sc.sky(dirv), np.array([0.5, 0.8, 0.9]) * c + np.array([0.7, 0.85, 0.9]) * (1.0 - c), atol=1e-15)
+    w, h = 8, 4
+    tex = np.arange(w * h * 3, dtype=np.float32).reshape(h, w, 3)
+    desc["sky"] = {"type": "Hdri", "c0": [0, 0, 0], "c1": [0, 0, 0], "width": w, "height": h, "texels": tex}
+    sc = oracle_mod.Scene(desc)
+    # straight up: lat = 0 -> y = h -> clamped to the last row; lon = atan2(0, 0) = 0 -> x = w/2
+    assert np.allclose(sc.sky([0.0, 1.0, 0.0]), tex[h - 1, w // 2])
+    # +x on the horizon: lat = pi/2 -> y = h/2; lon = 0 -> x = w/2.  -x: lon = pi -> x = w -> clamped to w - 1
+    assert np.allclose(sc.sky([1.0, 0.0, 0.0]), tex[h // 2, w // 2])
+    assert np.allclose(sc.sky([-1.0, 0.0, 0.0]), tex[h // 2, w - 1])
+    # +z: lon = pi/2 -> x = 3w/4;  straight down: lat = pi -> y = 0
+    assert np.allclose(sc.sky([0.0, 0.0, 1.0]), tex[h // 2, 3 * w // 4])
+    assert np.allclose(sc.sky([0.0, -1.0, 0.0]), tex[0, w // 2])

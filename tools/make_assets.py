@@ -145,7 +145,20 @@ def make_table(path=ROOT / "assets/round_table_with_tablecloth/13493_Round_Table
     return path
 
 
-MAKERS = {"dragon": make_dragon, "hdri": make_hdri, "doom": make_doom, "table": make_table}
+def make_vertex_colours(path=ROOT / "tests/golden/vertex_colours.ply", n=28, seed=0xC0105):
+    """A small vertex-coloured terrain inside +-8 units (committed fixture): the f32 production path's per-vertex albedo and smooth
+    normals against the oracle (doom.yml, the only reference scene with `albedo: {type: Vertex}`, works at +-700 and resolves to the
+    mixed-precision instantiation, so it never reaches the f32 mirrors)."""
+    rng = np.random.default_rng(seed)
+    u, v = np.meshgrid(np.arange(n) / (n - 1), np.arange(n) / (n - 1), indexing="ij")
+    hgt = 0.6 * _noise(u, v, rng, octaves=3)
+    p = np.stack([(u - 0.5) * 12.0, hgt, (v - 0.5) * 12.0], -1)
+    col = np.stack([128 + 120 * np.sin(9 * u), 128 + 120 * np.cos(7 * v), 128 + 120 * np.sin(5 * (u + v))], -1).clip(0, 255).astype(np.uint8)
+    write_ply(path, p.reshape(-1, 3), grid_faces(n, n, False, False), col.reshape(-1, 3))
+    return path
+
+
+MAKERS = {"dragon": make_dragon, "hdri": make_hdri, "doom": make_doom, "table": make_table, "vertex_colours": make_vertex_colours}
 
 
 def ensure(*names):
