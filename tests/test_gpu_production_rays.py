@@ -111,16 +111,25 @@ def check_closest(pb, oracle_mod, case, gsc, rays, kernel, max_diff_frac):
     same = p0 == p1
     hit = same & (p0 != oracle_mod.MISS)
     assert hit.any()
-    # t within 1e-4 relative (north_star).  A relative bound says nothing as t -> 0 (surface rays that dive back into the triangle
-    # they start on: t ~ 1e-8), so distances below the f32 resolution of the ray's own origin are held to that resolution instead:
-    # 16 ulp of the largest coordinate involved
-    err = np.abs(t1[hit] - t0[hit])
-    floor = 16 * 2.0**-23 * np.maximum(np.abs(o[hit]).max(axis=1), 1.0)
-    ok = (err <= 1e-4 * np.abs(t0[hit])) | (err <= floor)
-    worst = int(np.argmax(np.where(ok, 0.0, err)))
-    assert ok.all(), (f"{case.name} kernel {kernel}: {int((~ok).sum())} distances off, worst t0 {t0[hit][worst]!r} t1 {t1[hit][worst]!r} "
-                      f"origin {o[hit][worst]} prim {p0[hit][worst]}")
-    assert (err <= 1e-4 * np.abs(t0[hit])).mean() > 0.9999
+    # t within 1e-4 relative (north_star).  Where the forward bound fails the case must be ill-conditioned, not wrong: the ray is so
+    # nearly parallel to the primitive (or starts so close to it) that f32 cannot resolve t, and the reported hit point still lies ON
+    # the oracle's primitive to within 16 f32 ulps of the coordinates involved (backward error).  Such rays are rare (< 1e-4).
+    idx = np.nonzero(hit)[0]
+    err = np.abs(t1[idx] - t0[idx])
+    fwd = err <= 1e-4 * np.abs(t0[idx])
+    assert fwd.mean() > 0.9999, f"{case.name} kernel {kernel}: only {fwd.mean():.6f} of the distances within 1e-4 relative"
+    for i in idx[~fwd]:
+        is_tri, geom = gsc.prim_geometry(p0[i])
+        point = o[i] + d[i] * t1[i]
+        ulp = 2.0**-23 * max(np.abs(o[i]).max(), np.abs(point).max(), 1.0)
+        if is_tri:
+            nrm = geom[9:12] / np.linalg.norm(geom[9:12])
+            off = abs(nrm @ (point - geom[0:3]))
+        else:
+            off = abs(np.linalg.norm(point - geom[0:3]) - geom[3])
+            ulp = max(ulp, 2.0**-52 * geom[3] * 4)  # spheres are intersected in f64: the 1e6-radius "planes" resolve to ~1e-9
+        assert off <= 16 * ulp, (f"{case.name} kernel {kernel}: ray {i} t0 {t0[i]!r} t1 {t1[i]!r} prim {p0[i]}: the GPU's hit point is {off:.3g} "
+                                 f"off the primitive ({off / ulp:.1f} ulp)")
     assert np.all(np.isinf(t1[same & ~hit]))
     n_diff = int((~same).sum())
     assert n_diff <= max_diff_frac * len(p0), f"{case.name}: {n_diff} of {len(p0)} ids differ"
