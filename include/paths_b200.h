@@ -162,13 +162,16 @@ typedef struct {
     double ms_raygen, ms_extend, ms_shade, ms_shadow, ms_accumulate, ms_total; /* valid with time_kernels */
     uint64_t n_extend_launches, n_shadow_launches;
     double ms_device; /* device time of all render calls since reset: CUDA events on the launching stream, first to last kernel */
-    /* two-wide traversal stack overflows on this device since the library was loaded (a dropped subtree = a possibly missed hit);
-     * both tree builders bound the depth so that this stays 0, and the ray-level tests assert it */
-    uint64_t stack_overflows;
+    /* Debug-assert builds only (make EXTRA=-DPATHS_DEBUG_ASSERTS; debug_asserts = 1): two-wide traversal stack overflows (a dropped
+     * subtree = a possibly missed hit) and failed device assertions (queue positions inside their arrays) on this device since the
+     * library was loaded.  Release builds bound the tree depth on the host instead (both builders refuse trees deeper than 60 levels for
+     * the 64-entry stack) and report 0; the ray-level tests are run once under the debug-assert build (profiles/). */
+    uint64_t stack_overflows, assert_failures;
     /* which kernels this renderer launches: extend / visibility kernel for bounce rays (0 plain batches, 3 two-wide lane refill,
      * 16 four-wide), camera segment (1 = raygen fused with a plain-batch closest hit), shade scheduling (1 static round-robin,
      * 0 dynamic fetch), pass contexts in flight */
     int32_t extend_kernel, camera_kernel, shade_kernel, pass_contexts;
+    int32_t debug_asserts, _pad;
 } paths_stats;
 
 typedef struct {

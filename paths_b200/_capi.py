@@ -82,8 +82,8 @@ class Stats(C.Structure):
                 ("kernel_launches", C.c_uint64), ("passes", C.c_uint64), ("ms_raygen", C.c_double), ("ms_extend", C.c_double),
                 ("ms_shade", C.c_double), ("ms_shadow", C.c_double), ("ms_accumulate", C.c_double), ("ms_total", C.c_double),
                 ("n_extend_launches", C.c_uint64), ("n_shadow_launches", C.c_uint64),
-                ("ms_device", C.c_double), ("stack_overflows", C.c_uint64), ("extend_kernel", C.c_int32), ("camera_kernel", C.c_int32),
-                ("shade_kernel", C.c_int32), ("pass_contexts", C.c_int32)]
+                ("ms_device", C.c_double), ("stack_overflows", C.c_uint64), ("assert_failures", C.c_uint64), ("extend_kernel", C.c_int32),
+                ("camera_kernel", C.c_int32), ("shade_kernel", C.c_int32), ("pass_contexts", C.c_int32), ("debug_asserts", C.c_int32), ("_pad", C.c_int32)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

@@ -167,7 +167,13 @@ int resolve_precision(const paths_scene *s, int32_t precision) {
 extern "C" {
 
 const char *paths_last_error(void) { return g_err.c_str(); }
-const char *paths_version(void) { return "paths_b200 0.1 (sm_100a)"; }
+const char *paths_version(void) {
+#ifdef PATHS_DEBUG_ASSERTS
+    return "paths_b200 0.2 (sm_100a) +asserts";
+#else
+    return "paths_b200 0.2 (sm_100a)";
+#endif
+}
 
 paths_status paths_device_count(int32_t *count) {
     if (!count) return fail(PATHS_ERR_INVALID_ARG, "null count");
@@ -803,7 +809,7 @@ paths_status paths_group_get_stats(paths_group *g, paths_stats *out) {
         if (i == 0) tot = st;
         else {
             tot.samples += st.samples; tot.extend_rays += st.extend_rays; tot.shadow_rays += st.shadow_rays; tot.bad_samples += st.bad_samples;
-            tot.kernel_launches += st.kernel_launches; tot.passes += st.passes; tot.stack_overflows += st.stack_overflows;
+            tot.kernel_launches += st.kernel_launches; tot.passes += st.passes; tot.stack_overflows += st.stack_overflows; tot.assert_failures += st.assert_failures;
             tot.n_extend_launches += st.n_extend_launches; tot.n_shadow_launches += st.n_shadow_launches;
             tot.ms_raygen += st.ms_raygen; tot.ms_extend += st.ms_extend; tot.ms_shade += st.ms_shade; tot.ms_shadow += st.ms_shadow;
             tot.ms_accumulate += st.ms_accumulate; tot.ms_total += st.ms_total;

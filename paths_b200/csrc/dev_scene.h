@@ -88,17 +88,17 @@ struct DevCamera { // src/camera.rs:12-27 after CameraDescription::to_camera (sr
 };
 
 // One wavefront pass keeps n_slots camera paths in flight.  Slot i carries sample (s_base + i / n_local) of local pixel
-// (i % n_local).  Path state stays in its slot for the whole pass; queues hold slot indices.
+// (i % n_local).  The records a bounce reads and writes are DENSE BY QUEUE POSITION, not by slot: the shade kernel of bounce b writes
+// the ray and throughput of every surviving path at the position it takes in bounce b + 1's queue, so that the closest-hit kernel and
+// the next shade kernel stream contiguous lines (round 1 kept records in their slot and compacted indices only: after the first bounce
+// every access dragged half-used sectors through DRAM -- 84 B per ray for 52 useful in the closest-hit kernel, more bytes per entry in
+// shade bounce 1 than in bounce 0 -- and every ray fetch was a dependent load behind its queue entry).  Only the radiance record, which
+// few bounces touch, stays indexed by slot.  Buffers alternate with the bounce parity p = b & 1.
 template <typename R4> struct PathState {
-    // {origin, direction} are an interleaved pair, one 32-byte sector: ray_o[2 * slot], ray_d[2 * slot] with ray_d = ray_o + 1.  Bounce
-    // queues are sparse in slot order, and a 16-byte record of its own drags its dead neighbour's half of the sector through DRAM
-    // (ncu: 2.1 x the useful bytes on bounce 1).  hit and thr stay separate arrays: paired, the 16-byte hit write of the extend kernels
-    // became a partial-sector write that L2 completes by reading the sector first (+100 B/ray of DRAM traffic for the same run time).
-    R4 *ray_o; // origin xyz
-    R4 *ray_d; // direction xyz
-    R4 *hit;   // prim bits, t, bx, by
-    R4 *thr;   // throughput rgb, w = flags bits: loops | last_bounce_specular << 8
-    R4 *col;   // radiance rgb gathered so far, w = camera weight (src/camera.rs:91)
+    R4 *ray[2]; // ray[p][2 * pos] = {origin xyz, slot bits}, ray[p][2 * pos + 1] = {direction xyz, flags bits: loops | last_bounce_specular << 8}
+    R4 *thr[2]; // thr[p][pos] = throughput rgb (bounce 0: implicitly (1, 1, 1), never stored)
+    R4 *hit;    // hit[pos] = prim bits, t, bx, by of the bounce being traced
+    R4 *col;    // col[slot] = radiance rgb gathered so far, w = camera weight (src/camera.rs:91)
     // shadow-ray records, dense by shadow queue position
     R4 *sh_o;  // origin xyz, w = light index bits
     R4 *sh_d;  // direction xyz, w = slot bits
@@ -111,7 +111,6 @@ struct PassControl {
     uint32_t *scount;    // [max_bounces + 2] shadow rays emitted at bounce b
     uint32_t *ecount;    // [max_bounces + 2] environment NEE records emitted at bounce b (extension; second half of the shadow arrays)
     uint32_t *work;      // [PATHS_NWORK * (max_bounces + 2)] dynamic-fetch cursors, one per launch: extend, shade, shadow, env shadow
-    uint32_t *queue[2];  // slot indices, ping-pong
     unsigned long long *totals; // [0] extend rays [1] shadow rays [2] bad samples [3] samples
 };
 

@@ -200,12 +200,25 @@ struct HitF {
 
 #define PATHS_FAST_STACK 64
 // A two-wide traversal holds at most one postponed sibling per tree level, and both builders refuse trees deeper than 60 levels
-// (bvh_fast.cpp, bvh_device.cu), so the 64-entry stack cannot overflow.  Should it ever, the subtree is dropped AND counted here:
-// paths_stats.stack_overflows reports the total and the ray-level tests assert it is zero.  One copy per translation unit and device.
+// (bvh_fast.cpp: error; bvh_device.cu: falls back to the host builder), so the 64-entry stack cannot overflow.  The release kernels keep a
+// predicated store (an atomic in this cold branch cost 8-12 % of the closest-hit kernels' time: measured, profiles/r02c_ab.txt); the
+// debug-assert build (make EXTRA=-DPATHS_DEBUG_ASSERTS) counts every dropped push and every failed device assertion, and the ray-level
+// tests run once under it (paths_stats.stack_overflows / assert_failures, live only in that build).  One copy per translation unit.
 static __device__ unsigned long long g_stack_overflows = 0ull;
+static __device__ unsigned long long g_assert_failures = 0ull;
+#ifdef PATHS_DEBUG_ASSERTS
+#define PATHS_DASSERT(cond)                                   \
+    do {                                                      \
+        if (!(cond)) atomicAdd(&g_assert_failures, 1ull);     \
+    } while (0)
+#else
+#define PATHS_DASSERT(cond) ((void)0)
+#endif
 __device__ __forceinline__ void stack_push(int32_t *stack, int &sp, int32_t v) {
     if (sp < PATHS_FAST_STACK) stack[sp++] = v;
+#ifdef PATHS_DEBUG_ASSERTS
     else atomicAdd(&g_stack_overflows, 1ull);
+#endif
 }
 
 // ANY = true: return as soon as any primitive other than `skip_prim` is hit closer than tmax (shadow rays).

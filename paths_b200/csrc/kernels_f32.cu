@@ -15,7 +15,8 @@ paths_status trace_occluded_f32(const SceneDevice *sd, const double *o, const do
 }
 paths_status stack_overflows_f32(int device, unsigned long long *out, std::string &err) {
     PATHS_CU(cudaSetDevice(device));
-    return read_stack_overflows(out, err);
+    unsigned long long asserts = 0;
+    return read_stack_overflows(out, &asserts, err);
 }
 paths_status camera_rays_f32(const paths_camera &cam, int device, uint64_t seed, uint32_t sample, uint32_t x0, uint32_t y0, uint32_t w, uint32_t h,
                              double *o, double *d, double *weight, std::string &err) {

@@ -20,7 +20,8 @@ paths_status trace_occluded_mixed(const SceneDevice *sd, const double *o, const 
 }
 paths_status stack_overflows_f64(int device, unsigned long long *out, std::string &err) {
     PATHS_CU(cudaSetDevice(device));
-    return read_stack_overflows(out, err);
+    unsigned long long asserts = 0;
+    return read_stack_overflows(out, &asserts, err);
 }
 paths_status trace_closest_mixed(const SceneDevice *sd, const double *o, const double *d, size_t n, uint32_t *prim, double *t, double *bary,
                                  std::string &err) {

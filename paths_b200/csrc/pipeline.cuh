@@ -1,10 +1,11 @@
 // pipeline.cuh -- the wavefront kernels: raygen -> { extend -> shade -> shadow } x (max_bounces + 1) -> accumulate.
 //
 // Replaces the reference's thread pool (src/renderer.rs:34-110, src/worker.rs:43-87) and the per-path loop of
-// trace_ray (src/trace.rs:7-121).  One pass advances n_slots camera paths in lock step; path state lives in SoA
-// arrays of 16-byte (f32) / 32-byte (f64) records indexed by slot; live slots and shadow rays are compacted into
-// queues with one ballot + popc + atomicAdd per warp.  All kernels are persistent: a fixed grid of warps pulls
-// batches of 32 queue entries through an atomic cursor, so no host round trip is needed to learn queue lengths.
+// trace_ray (src/trace.rs:7-121).  One pass advances n_slots camera paths in lock step; the records of live paths are
+// 16-byte (f32) / 32-byte (f64) vectors kept DENSE BY QUEUE POSITION (dev_scene.h): the shade kernel compacts survivors
+// and their rays into the next bounce's arrays (ballot + popc, staged per warp in shared memory, one atomicAdd per flush),
+// so every kernel streams contiguous lines.  All kernels are persistent: a fixed grid of warps walks the queue, whose
+// length is read from device memory, so no host round trip is needed inside a pass.
 #pragma once
 #include "../../include/paths_b200.h"
 #include "dev_shade.cuh"
@@ -18,7 +19,7 @@ namespace paths {
 #define PATHS_LB_EXTEND 8
 #endif
 #ifndef PATHS_QBUF
-#define PATHS_QBUF 160u /* per-warp staging of next-queue entries in the shade kernel */
+#define PATHS_QBUF 96u /* per-warp staging of surviving paths (ray pair + throughput, 3 vectors each) in the shade kernel */
 #endif
 #ifndef PATHS_LB_SHADE
 #define PATHS_LB_SHADE 5
@@ -83,9 +84,9 @@ __global__ void __launch_bounds__(256) k_raygen(DevCamera cam, uint32_t k0, uint
         V3<R> o, d;
         R w;
         pixel_sample_ray<R>(cam, k0, k1, pixel, s_base + k, o, d, w);
-        st_rec(&ps.ray_o[2 * i], mk4(o.x, o.y, o.z, R(0)));
-        st_rec(&ps.ray_d[2 * i], mk4(d.x, d.y, d.z, R(0)));
-        st_rec(&ps.thr[i], mk4(R(1), R(1), R(1), bits_to_real(PATHS_FLAG_SPECULAR, R(0)))); // trace.rs:8-11
+        // bounce 0: queue position = slot; throughput (1, 1, 1) is implicit, "last bounce specular" starts true (trace.rs:8-11)
+        st_rec(&ps.ray[0][2 * i], mk4(o.x, o.y, o.z, bits_to_real(i, R(0))));
+        st_rec(&ps.ray[0][2 * i + 1], mk4(d.x, d.y, d.z, bits_to_real(PATHS_FLAG_SPECULAR, R(0))));
         st_rec(&ps.col[i], mk4(R(0), R(0), R(0), w));
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) pc.qcount[0] = n_slots;
@@ -93,8 +94,8 @@ __global__ void __launch_bounds__(256) k_raygen(DevCamera cam, uint32_t k0, uint
 
 // ------------------------------------------------------------------ extend: closest hit (src/scene.rs:172-197 -> src/bvh.rs:78-140)
 template <typename R, bool MIXED>
-__global__ void __launch_bounds__(128) k_extend(DevScene sc, PathState<typename Vec4T<R>::type> ps, const uint32_t *queue, const uint32_t *count_ptr,
-                                                uint32_t *cursor) {
+__global__ void __launch_bounds__(128) k_extend(DevScene sc, const typename Vec4T<R>::type *__restrict__ rays, typename Vec4T<R>::type *__restrict__ hits,
+                                                const uint32_t *count_ptr, uint32_t *cursor) {
     const uint32_t count = *count_ptr;
     const uint32_t lane = threadIdx.x & 31u;
     for (;;) {
@@ -102,17 +103,17 @@ __global__ void __launch_bounds__(128) k_extend(DevScene sc, PathState<typename 
         if (base >= count) break;
         uint32_t i = base + lane;
         if (i < count) {
-            uint32_t slot = queue ? queue[i] : i;
-            typename Vec4T<R>::type o = ld_rec(&ps.ray_o[2 * slot]), d = ld_rec(&ps.ray_d[2 * slot]);
+            const uint32_t slot = i; // records are dense by queue position
+            typename Vec4T<R>::type o = ld_rec(&rays[2 * i]), d = ld_rec(&rays[2 * i + 1]);
             if constexpr (IsF64<R>::value) {
                 Hit64 h = MIXED ? trace_mixed<false>(sc, mk3((double)o.x, (double)o.y, (double)o.z), mk3((double)d.x, (double)d.y, (double)d.z),
                                                      (double)__int_as_float(0x7f800000), 0xFFFFFFFFu)
                                 : trace_ref(sc, mk3((double)o.x, (double)o.y, (double)o.z), mk3((double)d.x, (double)d.y, (double)d.z));
-                st_rec(&ps.hit[slot], mk4(bits_to_real(h.prim, R(0)), R(h.t), R(h.bx), R(h.by)));
+                st_rec(&hits[slot], mk4(bits_to_real(h.prim, R(0)), R(h.t), R(h.bx), R(h.by)));
             } else {
                 HitF h = trace_fast<false>(sc, (float)o.x, (float)o.y, (float)o.z, (float)d.x, (float)d.y, (float)d.z, __int_as_float(0x7f800000),
                                            0xFFFFFFFFu);
-                st_rec(&ps.hit[slot], mk4(bits_to_real(h.prim, R(0)), R(h.t), R(h.bx), R(h.by)));
+                st_rec(&hits[slot], mk4(bits_to_real(h.prim, R(0)), R(h.t), R(h.bx), R(h.by)));
             }
         }
     }
@@ -121,7 +122,7 @@ __global__ void __launch_bounds__(128) k_extend(DevScene sc, PathState<typename 
 // ------------------------------------------------------------------ camera segment of the production path: raygen + closest hit
 // Primary rays of neighbouring slots are nearly parallel, so a warp's 32 rays walk the tree together: plain batches of 32
 // (no lane refill) are the faster schedule here (-2..3.5 % extend time), and generating the ray in the same kernel hides
-// raygen's 128 B/slot of HBM writes behind the traversal and saves reading the ray back (64 B/slot).
+// raygen's 64 B/slot of HBM writes behind the traversal and saves reading the ray back (32 B/slot).
 template <typename R> // float only; a template so that both translation units may include this header
 __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_camera_extend(DevScene sc, DevCamera cam, uint32_t k0, uint32_t k1, ShardInfo shard,
                                                                         uint32_t s_base, uint32_t n_slots, PathState<float4> ps, PassControl pc,
@@ -139,9 +140,9 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_camera_extend(DevScene
             V3<float> o, d;
             float w;
             pixel_sample_ray<float>(cam, k0, k1, pixel, s_base + k, o, d, w);
-            st_rec(&ps.ray_o[2 * i], make_float4(o.x, o.y, o.z, 0.0f));
-            st_rec(&ps.ray_d[2 * i], make_float4(d.x, d.y, d.z, 0.0f));
-            st_rec(&ps.thr[i], make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(PATHS_FLAG_SPECULAR))); // trace.rs:8-11
+            // bounce 0: queue position = slot; throughput (1, 1, 1) is implicit, "last bounce specular" starts true (trace.rs:8-11)
+            st_rec(&ps.ray[0][2 * i], make_float4(o.x, o.y, o.z, __uint_as_float(i)));
+            st_rec(&ps.ray[0][2 * i + 1], make_float4(d.x, d.y, d.z, __uint_as_float(PATHS_FLAG_SPECULAR)));
             st_rec(&ps.col[i], make_float4(0.0f, 0.0f, 0.0f, w));
             HitF h = trace_fast<false>(sc, o.x, o.y, o.z, d.x, d.y, d.z, __int_as_float(0x7f800000), 0xFFFFFFFFu);
             st_rec(&ps.hit[i], make_float4(__uint_as_float(h.prim), h.t, h.bx, h.by));
@@ -190,19 +191,22 @@ template <typename R> struct ShadeOut {
     bool alive, shadow, shadow2; // shadow2: environment NEE sample (extension)
     V3<R> sh_o, sh_d, sh_c, sh2_d, sh2_c;
     uint32_t light;
+    // the surviving path's next segment (alive): origin, direction, throughput, loops | specular flag
+    V3<R> next_o, next_d, next_thr;
+    uint32_t next_flags;
 };
 
 // LIGHTS: the scene has lights (next-event estimation is compiled in); EXT: any estimator extension is on.  The common kernels --
 // no extensions, with or without lights -- carry none of the other code and keep their registers for occupancy.
+// o4 = {origin, slot}, d4 = {direction, flags}, h4 = hit record of this segment, throughput = the path's weight so far.
 template <typename R, bool LIGHTS, bool EXT>
-__device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typename Vec4T<R>::type> &ps, uint32_t slot, uint32_t pixel, uint32_t S,
-                                           uint32_t k0, uint32_t k1, uint32_t max_bounces, uint32_t ext, unsigned long long *totals, ShadeOut<R> &out) {
+__device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typename Vec4T<R>::type> &ps, typename Vec4T<R>::type o4,
+                                           typename Vec4T<R>::type d4, typename Vec4T<R>::type h4, V3<R> throughput, uint32_t slot, uint32_t pixel,
+                                           uint32_t S, uint32_t k0, uint32_t k1, uint32_t max_bounces, uint32_t ext, unsigned long long *totals,
+                                           ShadeOut<R> &out) {
     typedef typename Vec4T<R>::type R4;
-    const V3<R> black = mk3<R>(R(0), R(0), R(0));
-    R4 o4 = ps.ray_o[2 * slot], d4 = ps.ray_d[2 * slot], h4 = ps.hit[slot], t4 = ps.thr[slot];
     V3<R> ro = mk3<R>(o4.x, o4.y, o4.z), rd = mk3<R>(d4.x, d4.y, d4.z);
-    V3<R> throughput = mk3<R>(t4.x, t4.y, t4.z);
-    uint32_t flags = real_to_bits(t4.w);
+    uint32_t flags = real_to_bits(d4.w);
     uint32_t loops = flags & 0xFFu;
     bool last_specular = (flags & PATHS_FLAG_SPECULAR) != 0;
     uint32_t prim = real_to_bits(h4.x);
@@ -361,26 +365,35 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
     }
     loops += 1;
     if (loops > max_bounces) return; // trace.rs:14-16
-    ps.ray_o[2 * slot] = mk4(new_origin.x, new_origin.y, new_origin.z, R(0));
-    ps.ray_d[2 * slot] = mk4(direction.x, direction.y, direction.z, R(0));
-    ps.thr[slot] = mk4(throughput.x, throughput.y, throughput.z, bits_to_real(loops | (is_specular ? PATHS_FLAG_SPECULAR : 0u), R(0)));
+    out.next_o = new_origin;
+    out.next_d = direction;
+    out.next_thr = throughput;
+    out.next_flags = loops | (is_specular ? PATHS_FLAG_SPECULAR : 0u);
     out.alive = true;
-    (void)black;
 }
 
+// Shade of bounce b: reads the dense records of parity b & 1 (ray pair, hit, throughput), writes the survivors' next segment densely
+// into parity (b + 1) & 1 at the positions they take in the next queue.
 template <typename R, bool LIGHTS, bool EXT>
-__global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LIGHTS || EXT) ? PATHS_LB_SHADE : PATHS_LB_SHADE_PLAIN)) k_shade(DevScene sc, PathState<typename Vec4T<R>::type> ps, ShardInfo shard, uint32_t s_base, uint32_t k0,
-                                               uint32_t k1, uint32_t max_bounces, uint32_t ext, const uint32_t *queue, uint32_t *queue_next,
+__global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LIGHTS || EXT) ? PATHS_LB_SHADE : PATHS_LB_SHADE_PLAIN)) k_shade(DevScene sc, PathState<typename Vec4T<R>::type> ps,
+                                               const typename Vec4T<R>::type *__restrict__ rin, const typename Vec4T<R>::type *__restrict__ tin,
+                                               typename Vec4T<R>::type *__restrict__ rout, typename Vec4T<R>::type *__restrict__ tout,
+                                               ShardInfo shard, uint32_t s_base, uint32_t k0,
+                                               uint32_t k1, uint32_t max_bounces, uint32_t ext, uint32_t bounce,
                                                const uint32_t *count_ptr, uint32_t *next_count, uint32_t *shadow_count, uint32_t *env_count,
                                                uint32_t env_base, uint32_t *cursor, unsigned long long *totals) {
+    typedef typename Vec4T<R>::type R4;
     const uint32_t count = *count_ptr;
     const uint32_t lane = threadIdx.x & 31u;
+    const bool first = bounce == 0; // queue position = slot, throughput (1, 1, 1) not stored
+    // rin / tin: this bounce's dense records (parity bounce & 1); rout / tout: the next bounce's (the other parity).  Passed as kernel
+    // parameters so that they are constant-bank operands, not registers (and never a dynamic index into the parameter block).
     // cursor == nullptr: batches of 32 entries are dealt to the warps of the grid round-robin (shading cost per entry is
     // uniform enough) -- no fetch atomic on the critical path; the next batch's records are prefetched into L2 meanwhile
-    __shared__ uint32_t qbuf_all[4][PATHS_QBUF];
-    uint32_t *qbuf = qbuf_all[threadIdx.x >> 5];
+    constexpr uint32_t QB = IsF64<R>::value ? 48u : PATHS_QBUF; // survivors staged per warp: {origin | slot, direction | flags} pairs, then throughputs
+    __shared__ R4 qbuf_all[4][3 * QB];
+    R4 *qbuf = qbuf_all[threadIdx.x >> 5];
     uint32_t fill = 0; // warp-uniform
-    typedef typename Vec4T<R>::type R4;
     constexpr uint32_t SBUF = LIGHTS ? (IsF64<R>::value ? 64u : 96u) : 1u; // shadow records staged per warp (origin | direction | contribution)
     __shared__ R4 sbuf_all[4][3 * SBUF];
     R4 *sbuf = sbuf_all[threadIdx.x >> 5];
@@ -395,9 +408,10 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LI
             static_base += warp_stride;
             uint32_t in = base + warp_stride + lane;
             if (in < count && base < count) {
-                uint32_t sn = queue ? __ldg(queue + in) : in;
-                prefetch_l2(ps.ray_o + 2 * sn); // {origin, direction}
-                prefetch_l2(ps.hit + sn); prefetch_l2(ps.thr + sn);
+                prefetch_l2(rin + 2 * (size_t)in); // {origin, direction}: one 32-byte sector (f32)
+                if (IsF64<R>::value) prefetch_l2(rin + 2 * (size_t)in + 1);
+                prefetch_l2(ps.hit + in);
+                if (!first) prefetch_l2(tin + in);
             }
         }
         if (base >= count) break;
@@ -406,13 +420,19 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LI
         out.alive = out.shadow = out.shadow2 = false;
         uint32_t slot = 0;
         if (i < count) {
-            slot = queue ? queue[i] : i;
+            R4 o4 = rin[2 * (size_t)i], d4 = rin[2 * (size_t)i + 1], h4 = ps.hit[i];
+            V3<R> thr = mk3<R>(R(1), R(1), R(1));
+            if (!first) {
+                R4 t4 = tin[i];
+                thr = mk3<R>(t4.x, t4.y, t4.z);
+            }
+            slot = real_to_bits(o4.w);
             uint32_t lp, k;
             shard.split(slot, lp, k);
             uint32_t pixel = shard.pixels ? shard.pixels[lp] : lp;
-            shade_path<R, LIGHTS, EXT>(sc, ps, slot, pixel, s_base + k, k0, k1, max_bounces, ext, totals, out);
+            shade_path<R, LIGHTS, EXT>(sc, ps, o4, d4, h4, thr, slot, pixel, s_base + k, k0, k1, max_bounces, ext, totals, out);
         }
-        if (LIGHTS) { // shadow records: staged per warp like the queue entries below, appended SBUF - 32 or more at a time
+        if (LIGHTS) { // shadow records: staged per warp like the survivors below, appended SBUF - 32 or more at a time
             const unsigned m = __ballot_sync(PATHS_FULL_MASK, out.shadow);
             if (out.shadow) {
                 const uint32_t k = sfill + __popc(m & ((1u << lane) - 1u));
@@ -426,6 +446,7 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LI
                 uint32_t sbase = 0;
                 if (lane == 0) sbase = atomicAdd(shadow_count, sfill);
                 sbase = __shfl_sync(PATHS_FULL_MASK, sbase, 0);
+                PATHS_DASSERT(sbase + sfill <= env_base);
                 for (uint32_t k = lane; k < sfill; k += 32u) {
                     ps.sh_o[sbase + k] = sbuf[k];
                     ps.sh_d[sbase + k] = sbuf[SBUF + k];
@@ -445,18 +466,25 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LI
                 ps.sh_c[epos] = mk4(out.sh2_c.x, out.sh2_c.y, out.sh2_c.z, R(0));
             }
         }
-        // surviving paths: gathered per warp in shared memory and appended to the next queue PATHS_QBUF - 32 or more at a time
-        // (one counter atomic and a few full-line stores per flush instead of one atomic per batch)
+        // surviving paths: their next segment is gathered per warp in shared memory and appended to the next bounce's dense arrays
+        // QB - 32 or more at a time (one counter atomic and full-line stores per flush instead of one atomic per batch)
         {
             const unsigned m = __ballot_sync(PATHS_FULL_MASK, out.alive);
-            if (out.alive) qbuf[fill + __popc(m & ((1u << lane) - 1u))] = slot;
+            if (out.alive) {
+                const uint32_t k = fill + __popc(m & ((1u << lane) - 1u));
+                qbuf[2 * k] = mk4(out.next_o.x, out.next_o.y, out.next_o.z, bits_to_real(slot, R(0)));
+                qbuf[2 * k + 1] = mk4(out.next_d.x, out.next_d.y, out.next_d.z, bits_to_real(out.next_flags, R(0)));
+                qbuf[2 * QB + k] = mk4(out.next_thr.x, out.next_thr.y, out.next_thr.z, R(0));
+            }
             fill += __popc(m);
-            if (fill > PATHS_QBUF - 32u) {
+            if (fill > QB - 32u) {
                 __syncwarp();
                 uint32_t qbase = 0;
                 if (lane == 0) qbase = atomicAdd(next_count, fill);
                 qbase = __shfl_sync(PATHS_FULL_MASK, qbase, 0);
-                for (uint32_t k = lane; k < fill; k += 32u) queue_next[qbase + k] = qbuf[k];
+                PATHS_DASSERT(qbase + fill <= env_base);
+                for (uint32_t k = lane; k < 2u * fill; k += 32u) rout[2 * (size_t)qbase + k] = qbuf[k];
+                for (uint32_t k = lane; k < fill; k += 32u) tout[qbase + k] = qbuf[2 * QB + k];
                 fill = 0;
                 __syncwarp();
             }
@@ -467,6 +495,7 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LI
         uint32_t sbase = 0;
         if (lane == 0) sbase = atomicAdd(shadow_count, sfill);
         sbase = __shfl_sync(PATHS_FULL_MASK, sbase, 0);
+        PATHS_DASSERT(sbase + sfill <= env_base);
         for (uint32_t k = lane; k < sfill; k += 32u) {
             ps.sh_o[sbase + k] = sbuf[k];
             ps.sh_d[sbase + k] = sbuf[SBUF + k];
@@ -478,7 +507,9 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LI
         uint32_t qbase = 0;
         if (lane == 0) qbase = atomicAdd(next_count, fill);
         qbase = __shfl_sync(PATHS_FULL_MASK, qbase, 0);
-        for (uint32_t k = lane; k < fill; k += 32u) queue_next[qbase + k] = qbuf[k];
+        PATHS_DASSERT(qbase + fill <= env_base);
+        for (uint32_t k = lane; k < 2u * fill; k += 32u) rout[2 * (size_t)qbase + k] = qbuf[k];
+        for (uint32_t k = lane; k < fill; k += 32u) tout[qbase + k] = qbuf[2 * QB + k];
     }
 }
 
@@ -553,8 +584,8 @@ __global__ void __launch_bounds__(128) k_shadow(DevScene sc, PathState<typename 
 // instead of waiting for the slowest ray of a batch of 32.  ROUNDS bounded traversal rounds run between two refill checks;
 // one round = up to three inner nodes, then at most one leaf.
 template <int ROUNDS, int MIN_REFILL, int KI = 3>
-__global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend_refill(DevScene sc, PathState<float4> ps, const uint32_t *queue, const uint32_t *count_ptr,
-                                                       uint32_t *cursor) {
+__global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend_refill(DevScene sc, const float4 *__restrict__ rays, float4 *__restrict__ hits,
+                                                       const uint32_t *count_ptr, uint32_t *cursor) {
     const uint32_t count = *count_ptr;
     const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
     const float4 *__restrict__ nodes = sc.fast_nodes;
@@ -575,8 +606,8 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend_refill(DevScene
             if (!has) {
                 uint32_t i = base + __popc(idle & lt);
                 if (i < count) {
-                    slot = queue ? queue[i] : i;
-                    float4 o = ld_rec(&ps.ray_o[2 * slot]), d = ld_rec(&ps.ray_d[2 * slot]);
+                    slot = i; // the hit record goes to the ray's own queue position
+                    float4 o = ld_rec(&rays[2 * (size_t)i]), d = ld_rec(&rays[2 * (size_t)i + 1]);
                     tv.init(o.x, o.y, o.z, d.x, d.y, d.z, __int_as_float(0x7f800000), sc.fast_root);
                     has = true;
                 }
@@ -591,7 +622,7 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend_refill(DevScene
                 for (int k = 0; k < KI && tv.node >= 0; k++) tv.inner(nodes, stack);
                 if (tv.node < 0 && tv.node != PATHS_TRAV_DONE) tv.leaf<false>(leaves, stack, 0xFFFFFFFFu);
                 if (tv.node == PATHS_TRAV_DONE) {
-                    st_rec(&ps.hit[slot], make_float4(__uint_as_float(tv.prim), tv.t, tv.bx, tv.by));
+                    st_rec(&hits[slot], make_float4(__uint_as_float(tv.prim), tv.t, tv.bx, tv.by));
                     has = false;
                 }
             }
@@ -743,8 +774,8 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_shadow4(DevScene sc, P
 // a round ends when fewer than MIN_INNER lanes still have an inner node to visit (one ballot per step), so that the leaf phase
 // runs with most lanes of the warp (ncu on k_extend4: triangle tests ran with 3.6 of 32 lanes, box tests with 13.8).
 template <int ROUNDS, int MIN_REFILL, int KI, int MIN_INNER>
-__global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend4s(DevScene sc, PathState<float4> ps, const uint32_t *queue, const uint32_t *count_ptr,
-                                                                   uint32_t *cursor) {
+__global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend4s(DevScene sc, const float4 *__restrict__ rays, float4 *__restrict__ hits,
+                                                                   const uint32_t *count_ptr, uint32_t *cursor) {
     extern __shared__ int32_t smem_stack[];
     int32_t *sstack = smem_stack + threadIdx.x;
     const uint32_t stride = blockDim.x;
@@ -768,8 +799,8 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend4s(DevScene sc, 
             if (!has) {
                 uint32_t i = base + __popc(idle & lt);
                 if (i < count) {
-                    slot = queue ? queue[i] : i;
-                    float4 o = ld_rec(&ps.ray_o[2 * slot]), d = ld_rec(&ps.ray_d[2 * slot]);
+                    slot = i; // the hit record goes to the ray's own queue position
+                    float4 o = ld_rec(&rays[2 * (size_t)i]), d = ld_rec(&rays[2 * (size_t)i + 1]);
                     tv.init(o.x, o.y, o.z, d.x, d.y, d.z, __int_as_float(0x7f800000), sc.fast4_root);
                     pend = 0;
                     has = true;
@@ -803,7 +834,7 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend4s(DevScene sc, 
                     pend = 0;
                 }
                 if (tv.node == PATHS_TRAV_DONE) {
-                    st_rec(&ps.hit[slot], make_float4(__uint_as_float(tv.prim), tv.t, tv.bx, tv.by));
+                    st_rec(&hits[slot], make_float4(__uint_as_float(tv.prim), tv.t, tv.bx, tv.by));
                     has = false;
                 }
             }

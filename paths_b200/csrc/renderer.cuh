@@ -89,8 +89,9 @@ struct TraceConfig {
 };
 
 // stack overflows of the two-wide kernels (dev_trace.cuh) since the library was loaded, on the current device
-static inline paths_status read_stack_overflows(unsigned long long *out, std::string &err) {
+static inline paths_status read_stack_overflows(unsigned long long *out, unsigned long long *asserts, std::string &err) {
     PATHS_CU(cudaMemcpyFromSymbol(out, g_stack_overflows, sizeof(unsigned long long)));
+    PATHS_CU(cudaMemcpyFromSymbol(asserts, g_assert_failures, sizeof(unsigned long long)));
     return PATHS_OK;
 }
 
@@ -192,7 +193,7 @@ template <typename R4> __global__ void k_stage_rays(const double *o, const doubl
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     typedef decltype(ray_pairs->x) S;
-    ray_pairs[2 * i] = mk4(S(o[3 * i]), S(o[3 * i + 1]), S(o[3 * i + 2]), S(0));
+    ray_pairs[2 * i] = mk4(S(o[3 * i]), S(o[3 * i + 1]), S(o[3 * i + 2]), bits_to_real(i, S(0))); // {origin | slot}
     ray_pairs[2 * i + 1] = mk4(S(d[3 * i]), S(d[3 * i + 1]), S(d[3 * i + 2]), S(0));
 }
 template <typename R4> __global__ void k_unstage_hits(const R4 *hit, DevScene sc, uint32_t n, uint32_t *prim, double *t, double *bary) {
@@ -280,16 +281,15 @@ paths_status trace_closest_impl(const SceneDevice *sd, const double *o, const do
             }
             PathState<R4> ps;
             std::memset(&ps, 0, sizeof(ps));
-            PATHS_CU(mem.get(&ps.ray_o, 2 * n));
-            ps.ray_d = ps.ray_o + 1;
+            PATHS_CU(mem.get(&ps.ray[0], 2 * n));
             PATHS_CU(mem.get(&ps.hit, n));
             PATHS_CU(mem.get(&ctl, 2));
             const uint32_t host_ctl[2] = {(uint32_t)n, 0u}; // queue length, fetch cursor
             PATHS_CU(cudaMemcpy(ctl, host_ctl, sizeof(host_ctl), cudaMemcpyHostToDevice));
-            k_stage_rays<R4><<<blocks, 128>>>(d_o, d_d, (uint32_t)n, ps.ray_o);
-            if (variant == 16) k_extend4s<1, 16, 16, 12><<<tc.grid4, 128, tc.smem4>>>(sd->view, ps, nullptr, ctl, ctl + 1);
-            else if (variant == 3) k_extend_refill<1, 16, 8><<<tc.grid_trace, 128>>>(sd->view, ps, nullptr, ctl, ctl + 1);
-            else k_extend<R, false><<<tc.grid_trace, 128>>>(sd->view, ps, nullptr, ctl, ctl + 1);
+            k_stage_rays<R4><<<blocks, 128>>>(d_o, d_d, (uint32_t)n, ps.ray[0]);
+            if (variant == 16) k_extend4s<1, 16, 16, 12><<<tc.grid4, 128, tc.smem4>>>(sd->view, ps.ray[0], ps.hit, ctl, ctl + 1);
+            else if (variant == 3) k_extend_refill<1, 16, 8><<<tc.grid_trace, 128>>>(sd->view, ps.ray[0], ps.hit, ctl, ctl + 1);
+            else k_extend<R, false><<<tc.grid_trace, 128>>>(sd->view, ps.ray[0], ps.hit, ctl, ctl + 1);
             k_unstage_hits<R4><<<blocks, 128>>>(ps.hit, sd->view, (uint32_t)n, d_p, d_t, d_b);
             staged = true;
         }

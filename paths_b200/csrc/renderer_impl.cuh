@@ -212,17 +212,15 @@ template <typename R> class RendererImpl : public RendererBase {
             PassCtx &x = ctx_[c];
             std::memset(&x.ps, 0, sizeof(x.ps));
             std::memset(&x.pc, 0, sizeof(x.pc));
-            // {origin, direction} is an interleaved pair (dev_scene.h)
-            if (alloc(&x.ps.ray_o, 2 * n_slots_max_) != PATHS_OK || alloc(&x.ps.hit, n_slots_max_) != PATHS_OK ||
-                alloc(&x.ps.thr, n_slots_max_) != PATHS_OK || alloc(&x.ps.col, n_slots_max_) != PATHS_OK)
-                return PATHS_ERR_CUDA;
-            x.ps.ray_d = x.ps.ray_o + 1;
+            // records dense by queue position, two parities (dev_scene.h): {origin | slot, direction | flags} pairs and throughputs
+            for (int p = 0; p < 2; p++)
+                if (alloc(&x.ps.ray[p], 2 * n_slots_max_) != PATHS_OK || alloc(&x.ps.thr[p], n_slots_max_) != PATHS_OK) return PATHS_ERR_CUDA;
+            if (alloc(&x.ps.hit, n_slots_max_) != PATHS_OK || alloc(&x.ps.col, n_slots_max_) != PATHS_OK) return PATHS_ERR_CUDA;
             // shadow records: one per path and bounce for light NEE, one more with environment NEE
             size_t n_shadow = n_slots_max_ * ((opts_.extensions & PATHS_EXT_ENV_NEE) ? 2 : 1);
             R4 **shadow[] = {&x.ps.sh_o, &x.ps.sh_d, &x.ps.sh_c};
             for (R4 **p : shadow)
                 if (alloc(p, n_shadow) != PATHS_OK) return PATHS_ERR_CUDA;
-            if (alloc(&x.pc.queue[0], n_slots_max_) != PATHS_OK || alloc(&x.pc.queue[1], n_slots_max_) != PATHS_OK) return PATHS_ERR_CUDA;
             if (alloc(&x.ctl, n_ctl_) != PATHS_OK) return PATHS_ERR_CUDA;
             x.pc.qcount = x.ctl;
             x.pc.scount = x.ctl + nb;
@@ -256,19 +254,20 @@ template <typename R> class RendererImpl : public RendererBase {
         return PATHS_OK;
     }
 
-    void launch_extend(const uint32_t *q, uint32_t b) {
+    void launch_extend(uint32_t b) {
+        const R4 *q = ps_.ray[b & 1u]; // the dense ray records this bounce reads
         if constexpr (!IsF64<R>::value) {
             const uint32_t *cnt = pc_.qcount + b;
             uint32_t *cur = pc_.work + PATHS_NWORK * b;
             int vsel = (b == 0 && tc_.variant_b0 >= 0) ? tc_.variant_b0 : tc_.variant;
             switch (vsel) { // 0 = one batch of 32 rays per warp at a time (k_extend), kept as the plain baseline
-            case 3: k_extend_refill<1, 16, 8><<<tc_.grid_trace, 128, 0, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
-            case 16: k_extend4s<1, 16, 16, 12><<<tc_.grid4, 128, tc_.smem4, cs_>>>(sd_->view, ps_, q, cnt, cur); return;
+            case 3: k_extend_refill<1, 16, 8><<<tc_.grid_trace, 128, 0, cs_>>>(sd_->view, q, ps_.hit, cnt, cur); return;
+            case 16: k_extend4s<1, 16, 16, 12><<<tc_.grid4, 128, tc_.smem4, cs_>>>(sd_->view, q, ps_.hit, cnt, cur); return;
             default: break;
             }
         }
-        if (mixed_) k_extend<R, true><<<tc_.grid_trace, 128, 0, cs_>>>(sd_->view, ps_, q, pc_.qcount + b, pc_.work + PATHS_NWORK * b);
-        else k_extend<R, false><<<tc_.grid_trace, 128, 0, cs_>>>(sd_->view, ps_, q, pc_.qcount + b, pc_.work + PATHS_NWORK * b);
+        if (mixed_) k_extend<R, true><<<tc_.grid_trace, 128, 0, cs_>>>(sd_->view, q, ps_.hit, pc_.qcount + b, pc_.work + PATHS_NWORK * b);
+        else k_extend<R, false><<<tc_.grid_trace, 128, 0, cs_>>>(sd_->view, q, ps_.hit, pc_.qcount + b, pc_.work + PATHS_NWORK * b);
     }
     // visibility of the records [0, *count) of `ps`'s shadow arrays; `cursor` is this launch's dynamic-fetch counter
     void launch_shadow(const PathState<R4> &ps, const uint32_t *count, uint32_t *cursor) {
@@ -308,20 +307,18 @@ template <typename R> class RendererImpl : public RendererBase {
             toc();
         }
         for (uint32_t b = 0; b < nb; b++) {
-            const uint32_t *q = b == 0 ? nullptr : pc_.queue[b & 1];
             tic(1);
             if (b == 0 && fused_camera) {
                 if constexpr (!IsF64<R>::value)
                     k_camera_extend<float><<<tc_.grid_camera, 128, 0, cs_>>>(sd_->view, cam_, k0, k1, shard, s_base, n_slots, ps_, pc_, pc_.work);
-            } else launch_extend(q, b);
+            } else launch_extend(b);
             toc();
             stats_.n_extend_launches++;
             tic(2);
             {
                 uint32_t *shade_cursor = shade_variant_ == 1 ? nullptr : pc_.work + PATHS_NWORK * b + 1;
-                uint32_t *qn = pc_.queue[(b + 1) & 1];
                 // three instantiations: every extension compiled in (lights or not) / lights only / neither
-#define PATHS_SHADE_ARGS sd_->view, ps_, shard, s_base, k0, k1, opts_.max_bounces, opts_.extensions, q, qn, pc_.qcount + b, pc_.qcount + b + 1, pc_.scount + b, pc_.ecount + b, (uint32_t)n_slots_max_, shade_cursor, pc_.totals
+#define PATHS_SHADE_ARGS sd_->view, ps_, ps_.ray[b & 1u], ps_.thr[b & 1u], ps_.ray[(b + 1u) & 1u], ps_.thr[(b + 1u) & 1u], shard, s_base, k0, k1, opts_.max_bounces, opts_.extensions, b, pc_.qcount + b, pc_.qcount + b + 1, pc_.scount + b, pc_.ecount + b, (uint32_t)n_slots_max_, shade_cursor, pc_.totals
                 if (opts_.extensions != 0) {
                     if (sd_->view.n_lights > 0) k_shade<R, true, true><<<grid_shade_, 128, 0, cs_>>>(PATHS_SHADE_ARGS);
                     else k_shade<R, false, true><<<grid_shade_, 128, 0, cs_>>>(PATHS_SHADE_ARGS);
@@ -586,10 +583,14 @@ template <typename R> class RendererImpl : public RendererBase {
         stats_.bad_samples = t[2];
         stats_.samples = t[3];
         {
-            unsigned long long ovf = 0;
-            paths_status so = read_stack_overflows(&ovf, err);
+            unsigned long long ovf = 0, asserts = 0;
+            paths_status so = read_stack_overflows(&ovf, &asserts, err);
             if (so != PATHS_OK) return so;
             stats_.stack_overflows = ovf;
+            stats_.assert_failures = asserts;
+#ifdef PATHS_DEBUG_ASSERTS
+            stats_.debug_asserts = 1;
+#endif
         }
         stats_.extend_kernel = tc_.variant;
         stats_.camera_kernel = tc_.variant_b0;
