@@ -62,6 +62,7 @@ struct paths_renderer {
     uint64_t seed = 0;
     uint32_t rank = 0, world = 1;
     int32_t device = 0;
+    paths_render_opts opts; // as resolved at creation (precision AUTO already replaced)
     ~paths_renderer() { delete impl; }
 };
 
@@ -647,6 +648,7 @@ paths_status paths_renderer_create(paths_scene *s, const paths_camera *cam, cons
     r->rank = opts.rank;
     r->world = std::max<uint32_t>(opts.world, 1);
     r->device = opts.device;
+    r->opts = opts;
     *out = r;
     return PATHS_OK;
     PATHS_GUARD_END
@@ -903,11 +905,16 @@ paths_status paths_renderer_get_progress(paths_renderer *r, uint32_t *samples_pe
 // ---- checkpoint / resume: the estimator (sum + count per pixel) and the position in the sample schedule are the whole state
 namespace {
 struct CheckpointHeader {
-    char magic[8]; // "PATHSCK1"
+    char magic[8]; // "PATHSCK2"
     uint32_t width, height;
     uint32_t samples_done;
-    uint32_t reserved;
+    uint32_t max_bounces;
     uint64_t seed;
+    // everything else that decides which estimator the sums belong to: resuming under other settings would silently mix estimators
+    uint32_t extensions;
+    int32_t precision, shard_mode;
+    uint32_t rank, world;
+    uint32_t reserved;
 };
 } // namespace
 
@@ -923,11 +930,17 @@ paths_status paths_renderer_save_checkpoint(paths_renderer *r, const char *path)
     if (st != PATHS_OK) return fail(st, r->impl->err);
     CheckpointHeader h;
     std::memset(&h, 0, sizeof(h));
-    std::memcpy(h.magic, "PATHSCK1", 8);
+    std::memcpy(h.magic, "PATHSCK2", 8);
     h.width = r->w;
     h.height = r->h;
     h.samples_done = done;
     h.seed = r->seed;
+    h.max_bounces = r->opts.max_bounces;
+    h.extensions = r->opts.extensions;
+    h.precision = r->opts.precision;
+    h.shard_mode = r->world > 1 ? r->opts.shard_mode : 0;
+    h.rank = r->rank;
+    h.world = r->world;
     FILE *f = std::fopen(path, "wb");
     if (!f) return fail(PATHS_ERR_IO, std::string("cannot open ") + path);
     bool ok = std::fwrite(&h, sizeof(h), 1, f) == 1 && std::fwrite(sums.data(), sizeof(double), sums.size(), f) == sums.size();
@@ -943,7 +956,7 @@ paths_status paths_renderer_load_checkpoint(paths_renderer *r, const char *path)
     if (!f) return fail(PATHS_ERR_IO, std::string("cannot open ") + path);
     CheckpointHeader h;
     std::vector<double> sums;
-    bool ok = std::fread(&h, sizeof(h), 1, f) == 1 && std::memcmp(h.magic, "PATHSCK1", 8) == 0;
+    bool ok = std::fread(&h, sizeof(h), 1, f) == 1 && std::memcmp(h.magic, "PATHSCK2", 8) == 0;
     if (ok && (h.width != r->w || h.height != r->h)) {
         std::fclose(f);
         return fail(PATHS_ERR_INVALID_ARG, "checkpoint was taken at another image size");
@@ -951,6 +964,12 @@ paths_status paths_renderer_load_checkpoint(paths_renderer *r, const char *path)
     if (ok && h.seed != r->seed) {
         std::fclose(f);
         return fail(PATHS_ERR_INVALID_ARG, "checkpoint was taken with another seed: resuming would repeat or skip samples");
+    }
+    if (ok && (h.max_bounces != r->opts.max_bounces || h.extensions != r->opts.extensions || h.precision != r->opts.precision ||
+               h.world != r->world || h.rank != r->rank || (r->world > 1 && h.shard_mode != r->opts.shard_mode))) {
+        std::fclose(f);
+        return fail(PATHS_ERR_INVALID_ARG, "checkpoint was taken under other render options (max_bounces, extensions, precision or shard layout): "
+                                           "resuming would mix two estimators");
     }
     if (ok) {
         sums.resize((size_t)h.width * h.height * 4);

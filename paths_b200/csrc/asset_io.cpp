@@ -240,6 +240,15 @@ paths_status load_ply(const std::string &path, LoadedModel &out, std::string &er
             return PATHS_ERR_PARSE;
         }
         bool colours = is_vertex && ir >= 0 && ig >= 0 && ib >= 0; // src/ply.rs:59-71
+        // a header-declared count is checked against what the rest of the file can hold before anything loops over it or allocates:
+        // every row needs at least one byte per property (ascii: a character; binary: the smallest scalar / list count)
+        {
+            const size_t left = ascii ? (size_t)((const char *)end - ap) : (size_t)(end - p);
+            if (el.props.empty() ? el.count != 0 : el.count > left / el.props.size() + 1) {
+                err = path + ": element '" + el.name + "' declares more rows than the file can hold";
+                return PATHS_ERR_PARSE;
+            }
+        }
         std::vector<double> vals(el.props.size());
         std::vector<double> list;
         for (size_t row = 0; row < el.count; row++) {
@@ -266,6 +275,7 @@ paths_status load_ply(const std::string &path, LoadedModel &out, std::string &er
                         p += n;
                     }
                     bool keep = is_face && (pr.name == "vertex_indices" || pr.name == "vertex_index");
+                    if (!(cnt >= 0.0 && cnt <= 1048576.0)) { err = path + ": list length out of range"; return PATHS_ERR_PARSE; }
                     for (int c = 0; c < (int)cnt; c++) {
                         double v;
                         if (ascii) {
@@ -291,7 +301,10 @@ paths_status load_ply(const std::string &path, LoadedModel &out, std::string &er
                 }
             } else if (is_face) {
                 if (list.size() < 3) { err = path + ": face with fewer than 3 indices"; return PATHS_ERR_PARSE; }
-                for (int c = 0; c < 3; c++) out.faces.push_back((uint32_t)list[c]); // src/ply.rs:72-75 keeps the first three
+                for (int c = 0; c < 3; c++) { // src/ply.rs:72-75 keeps the first three
+                    if (!(list[c] >= 0.0 && list[c] <= 4294967294.0)) { err = path + ": face index out of range"; return PATHS_ERR_PARSE; }
+                    out.faces.push_back((uint32_t)list[c]);
+                }
             }
         }
     }
@@ -323,6 +336,16 @@ paths_status load_hdr(const std::string &path, uint32_t &w, uint32_t &h, std::ve
     if (!found || w == 0 || h == 0) {
         err = path + ": no Radiance resolution line";
         return PATHS_ERR_PARSE;
+    }
+    // the resolution line is checked against the bytes that follow before anything is allocated: a flat scanline takes 4 bytes per
+    // pixel, a run-length encoded one at least 4 + 4 * ceil(w / 127) * 2
+    {
+        const size_t left = data.size() - pos;
+        const size_t min_row = std::min<size_t>((size_t)w * 4, 4 + 8 * (((size_t)w + 126) / 127));
+        if ((size_t)h > left / std::max<size_t>(min_row, 1) + 1 || (uint64_t)w * h > (1ull << 31)) {
+            err = path + ": resolution line declares more pixels than the file can hold";
+            return PATHS_ERR_PARSE;
+        }
     }
     std::vector<unsigned char> rgbe((size_t)w * h * 4);
     const unsigned char *d = (const unsigned char *)data.data();

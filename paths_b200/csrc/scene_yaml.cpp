@@ -183,8 +183,13 @@ paths_status load_scene_yaml(const std::string &yaml_path, const std::string &as
     const YamlNode *cam = c.req(&root, "camera");
     std::memset(&out.camera, 0, sizeof(out.camera));
     if (cam) {
-        out.camera.image_width = (uint32_t)c.fnum(cam, "image_width");
-        out.camera.image_height = (uint32_t)c.fnum(cam, "image_height");
+        {
+            const double iw = c.fnum(cam, "image_width"), ih = c.fnum(cam, "image_height");
+            const bool in_range = iw >= 1.0 && iw <= 65536.0 && ih >= 1.0 && ih <= 65536.0; // false for NaN too
+            if (!in_range) c.fail(cam, "image_width / image_height out of range");
+            out.camera.image_width = in_range ? (uint32_t)iw : 0u; // the cast is only taken where it is defined
+            out.camera.image_height = in_range ? (uint32_t)ih : 0u;
+        }
         c.vec(c.req(cam, "location"), out.camera.location);
         const YamlNode *o = c.req(cam, "orientation");
         out.camera.pitch = c.fnum(o, "pitch");

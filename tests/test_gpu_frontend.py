@@ -138,5 +138,14 @@ def test_checkpoint_resume_is_bit_identical(pb, tmp_path):
         c.load_checkpoint(ck)  # another seed would repeat samples
     with pytest.raises(pb.PathsError):
         c.load_checkpoint(tmp_path / "missing.ck")
+    # the header also records what else decides the estimator: other bounce limits, extensions, precision or shard layouts are refused
+    for kw in (dict(max_bounces=3), dict(extensions=pb.EXT_NEE_ALL_LIGHTS), dict(precision=64), dict(rank=0, world=2)):
+        opts = dict(precision=32, seed=11)
+        opts.update(kw)
+        d = pb.Renderer(sc.camera, sc, **opts)
+        with pytest.raises(pb.PathsError) as e:
+            d.load_checkpoint(ck)
+        assert "other render options" in str(e.value)
+        d.shutdown()
     for r in (a, b, c):
         r.shutdown()

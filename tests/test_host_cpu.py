@@ -273,3 +273,20 @@ def test_abi_rejects_null_and_out_of_range_arguments():
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "UNEXPECTED OK: []" in r.stdout
     assert r.stdout.count("-> 1 ") >= 40  # PATHS_ERR_INVALID_ARG with a message each
+
+
+def test_rust_binding_declares_every_symbol():
+    # bindings/rust/paths-b200-sys is shipped unbuilt (no rustc here): keep its extern block and struct mirrors in step with the header
+    header = (ROOT / "include" / "paths_b200.h").read_text()
+    declared = set(re.findall(r"\b(paths_[a-z0-9_]+)\s*\(", header)) - {"paths_status"}
+    rs = (ROOT / "bindings" / "rust" / "paths-b200-sys" / "src" / "lib.rs").read_text()
+    bound = set(re.findall(r"pub fn (paths_[a-z0-9_]+)\s*\(", rs))
+    assert declared == bound, f"header vs Rust extern block: {sorted(declared ^ bound)}"
+    # field counts of the #[repr(C)] mirrors == field counts of the ctypes mirrors (which the layout test above pins to the header)
+    import paths_b200._capi as c
+
+    for rust_name, ct in (("paths_stats", c.Stats), ("paths_render_opts", c.RenderOpts), ("paths_camera", c.Camera), ("paths_scene_info", c.SceneInfo)):
+        body = re.search(r"pub struct %s \{(.*?)\n\}" % rust_name, rs, re.S).group(1)
+        body = re.sub(r"//.*", "", body)
+        fields = re.findall(r"pub\s+(\w+)\s*:", body)
+        assert [f.rstrip("_") for f in fields] == [n for n, _ in ct._fields_], rust_name

@@ -48,7 +48,8 @@ CASES = {
     "trunc_header.ply": (PLY[:60], "not a PLY"),
     "bad_index.ply": (PLY[:-12] + struct.pack("<3i", 0, 1, 99), "out of range"),
     "neg_index.ply": (PLY[:-12] + struct.pack("<3i", 0, -1, 2), "out of range"),
-    "huge_count.ply": (PLY.replace(b"element vertex 3", b"element vertex 4000000000"), "truncated"),
+    "huge_count.ply": (PLY.replace(b"element vertex 3", b"element vertex 4000000000"), "more rows than the file can hold"),
+    "endless_element.ply": (PLY.replace(b"end_header", b"element junk 18446744073709551615\nend_header"), "more rows than the file can hold"),
     "empty.ply": (b"", "not a PLY"),
     "garbage.ply": (bytes(range(256)), "not a PLY"),
     "good.obj": (OBJ + b"f 1 2 3\n", 1),
@@ -125,6 +126,7 @@ HDR_CASES = {
     "bad_magic.hdr": (b"P6\n8 2\n255\n" + bytes(48), False),
     "zero_size.hdr": (b"#?RADIANCE\nFORMAT=32-bit_rle_rgbe\n\n-Y 0 +X 0\n", False),
     "empty.hdr": (b"", False),
+    "huge_resolution.hdr": (b"#?RADIANCE\nFORMAT=32-bit_rle_rgbe\n\n-Y 4000000000 +X 4000000000\n" + bytes(64), False),  # refused before allocating
 }
 
 
