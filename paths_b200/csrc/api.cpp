@@ -761,15 +761,19 @@ paths_status paths_group_render(paths_group *g, uint32_t spp) {
         paths_status bad = PATHS_OK;
         std::string why;
         for (paths_renderer *r : g->r) {
-            paths_status st = r->impl->combine(0, false);
+            paths_status st = r->impl->combine_post(0);
             if (st != PATHS_OK && bad == PATHS_OK) {
                 bad = st;
                 why = r->impl->err;
             }
         }
-        ncclResult_t rr = api->GroupEnd();
+        ncclResult_t rr = api->GroupEnd(); // the grouped sends / receives / reduces are enqueued on the ranks' streams here
         if (bad != PATHS_OK) return fail(bad, why);
         if (rr != ncclSuccess) return fail(PATHS_ERR_NCCL, std::string("ncclGroupEnd: ") + api->GetErrorString(rr));
+        for (paths_renderer *r : g->r) {
+            paths_status st = r->impl->combine_finish(0);
+            if (st != PATHS_OK) return fail(st, r->impl->err);
+        }
     }
     for (paths_renderer *r : g->r) {
         paths_status st = r->impl->sync();

@@ -842,6 +842,74 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend4s(DevScene sc, 
     }
 }
 
+// Two-wide, speculative: the schedule of k_extend4s over two-wide nodes and a local stack.  A lane that reaches a leaf parks it and keeps
+// descending from its stack; the inner phase ends when fewer than MIN_INNER lanes still have an inner node to visit.
+template <int ROUNDS, int MIN_REFILL, int KI, int MIN_INNER>
+__global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_extend2s(DevScene sc, const float4 *__restrict__ rays, float4 *__restrict__ hits,
+                                                                   const uint32_t *count_ptr, uint32_t *cursor) {
+    const uint32_t count = *count_ptr;
+    const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    const float4 *__restrict__ nodes = sc.fast_nodes;
+    const float4 *__restrict__ leaves = sc.fast_leaves;
+    int32_t stack[PATHS_FAST_STACK];
+    TravF tv;
+    tv.node = PATHS_TRAV_DONE;
+    bool has = false, exhausted = false;
+    uint32_t slot = 0;
+    int32_t pend = 0;
+    for (;;) {
+        unsigned idle = __ballot_sync(PATHS_FULL_MASK, !has);
+        int n = __popc(idle);
+        if (!exhausted && n >= MIN_REFILL) {
+            int leader = __ffs(idle) - 1;
+            uint32_t base = 0;
+            if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)n);
+            base = __shfl_sync(PATHS_FULL_MASK, base, leader);
+            if (!has) {
+                uint32_t i = base + __popc(idle & lt);
+                if (i < count) {
+                    slot = i;
+                    float4 o = ld_rec(&rays[2 * (size_t)i]), d = ld_rec(&rays[2 * (size_t)i + 1]);
+                    tv.init(o.x, o.y, o.z, d.x, d.y, d.z, __int_as_float(0x7f800000), sc.fast_root);
+                    pend = 0;
+                    has = true;
+                }
+            }
+            exhausted = base + (uint32_t)n >= count;
+        }
+        if (!__any_sync(PATHS_FULL_MASK, has)) break;
+#pragma unroll 1
+        for (int r = 0; r < ROUNDS; r++) {
+            const int n_has = __popc(__ballot_sync(PATHS_FULL_MASK, has));
+#pragma unroll 1
+            for (int k = 0; k < KI; k++) {
+                bool inner = has && tv.node >= 0;
+                int n_inner = __popc(__ballot_sync(PATHS_FULL_MASK, inner));
+                if (n_inner == 0 || (n_inner < MIN_INNER && n_inner < n_has)) break;
+                if (inner) tv.inner(nodes, stack);
+                if (has && pend == 0 && tv.node < 0 && tv.node != PATHS_TRAV_DONE) {
+                    pend = tv.node;
+                    tv.node = tv.pop(stack);
+                }
+            }
+            if (has) {
+                if (pend == 0 && tv.node < 0 && tv.node != PATHS_TRAV_DONE) { // reached while the inner phase was cut short
+                    pend = tv.node;
+                    tv.node = tv.pop(stack);
+                }
+                if (pend != 0) {
+                    tv.leaf_test<false>(leaves, pend, 0xFFFFFFFFu);
+                    pend = 0;
+                }
+                if (tv.node == PATHS_TRAV_DONE) {
+                    st_rec(&hits[slot], make_float4(__uint_as_float(tv.prim), tv.t, tv.bx, tv.by));
+                    has = false;
+                }
+            }
+        }
+    }
+}
+
 // ------------------------------------------------------------------ accumulate (src/pixels.rs:6-31,49-51; worker.rs:76 applies the camera weight)
 template <typename R>
 __global__ void __launch_bounds__(256) k_accumulate(PathState<typename Vec4T<R>::type> ps, ShardInfo shard, uint32_t spp_pass,

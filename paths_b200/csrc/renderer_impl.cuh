@@ -4,6 +4,10 @@
 
 #include "renderer.cuh"
 
+#ifndef PATHS_EXTEND2_KI
+#define PATHS_EXTEND2_KI 12
+#endif
+
 namespace paths {
 
 template <typename R> class RendererImpl : public RendererBase {
@@ -52,6 +56,7 @@ template <typename R> class RendererImpl : public RendererBase {
     uint32_t *peer_pixels_ = nullptr; // root, tile shards: pixel lists of the other ranks, concatenated in rank order
     int peer_pixels_root_ = -1;
     std::vector<uint32_t> peer_counts_;
+    size_t scatter_total_ = 0;
     uint32_t *pixels_ = nullptr; // tile shard: local -> global pixel
     // interactive front half (renderer.rs:143-192): column sweeps from the centre outwards, preview grid
     uint32_t *sweep_pixels_ = nullptr; // scratch local -> global table for column / preview passes [npix_]
@@ -261,7 +266,11 @@ template <typename R> class RendererImpl : public RendererBase {
             uint32_t *cur = pc_.work + PATHS_NWORK * b;
             int vsel = (b == 0 && tc_.variant_b0 >= 0) ? tc_.variant_b0 : tc_.variant;
             switch (vsel) { // 0 = one batch of 32 rays per warp at a time (k_extend), kept as the plain baseline
+#ifdef PATHS_EXTEND2_SPEC
+            case 3: k_extend2s<1, 16, PATHS_EXTEND2_KI, PATHS_EXTEND2_SPEC><<<tc_.grid_trace, 128, 0, cs_>>>(sd_->view, q, ps_.hit, cnt, cur); return;
+#else
             case 3: k_extend_refill<1, 16, 8><<<tc_.grid_trace, 128, 0, cs_>>>(sd_->view, q, ps_.hit, cnt, cur); return;
+#endif
             case 16: k_extend4s<1, 16, 16, 12><<<tc_.grid4, 128, tc_.smem4, cs_>>>(sd_->view, q, ps_.hit, cnt, cur); return;
             default: break;
             }
@@ -489,8 +498,28 @@ template <typename R> class RendererImpl : public RendererBase {
     // a dense buffer and sends it, the root receives the others' buffers in one NCCL group and scatters them -- bit-identical to one GPU
     // and 1/world of the bytes a reduce of full frames moves.
     paths_status combine(int32_t root, bool wait) override {
+        paths_status st = combine_post(root);
+        if (st == PATHS_OK) st = combine_finish(root);
+        if (st != PATHS_OK) return st;
+        return wait ? sync() : PATHS_OK;
+    }
+    paths_status combine_finish(int32_t root) override {
         const uint32_t world = std::max<uint32_t>(opts_.world, 1);
-        if (world == 1) return wait ? sync() : PATHS_OK; // nothing to combine: the estimator is the frame
+        if (world == 1 || !comm_) return PATHS_OK;
+        PATHS_CU(cudaSetDevice(sd_->device));
+        const bool is_root = (uint32_t)root == opts_.rank;
+        if (is_root && opts_.shard_mode == PATHS_SHARD_TILES && scatter_total_ > 0) {
+            k_scatter_pixels<R4><<<(unsigned)((scatter_total_ + 255) / 256), 256, 0, stream_>>>(pack_, peer_pixels_, (uint32_t)scatter_total_, frame_);
+            stats_.kernel_launches++;
+        }
+        PATHS_CU(cudaGetLastError());
+        frame_valid_ = is_root;
+        return PATHS_OK;
+    }
+    paths_status combine_post(int32_t root) override {
+        const uint32_t world = std::max<uint32_t>(opts_.world, 1);
+        scatter_total_ = 0;
+        if (world == 1) return PATHS_OK; // nothing to combine: the estimator is the frame
         if (!comm_) {
             err = "no communicator attached: call paths_renderer_attach_comm (or render through a paths_group)";
             return PATHS_ERR_INVALID_ARG;
@@ -518,6 +547,7 @@ template <typename R> class RendererImpl : public RendererBase {
             }
             if (n_local_ > 0) {
                 k_pack_pixels<R4><<<(n_local_ + 255) / 256, 256, 0, stream_>>>(sums_, pixels_, n_local_, pack_);
+                stats_.kernel_launches++;
                 PATHS_NCCL(api, Send(pack_, (size_t)n_local_ * 4, dt, root, comm_, stream_));
             }
         } else {
@@ -554,12 +584,10 @@ template <typename R> class RendererImpl : public RendererBase {
             }
             PATHS_NCCL(api, GroupEnd());
             total = off;
-            if (total > 0) k_scatter_pixels<R4><<<(unsigned)((total + 255) / 256), 256, 0, stream_>>>(pack_, peer_pixels_, (uint32_t)total, frame_);
+            scatter_total_ = total; // scattered into frame_ by combine_finish, once the receives are really enqueued
         }
         PATHS_CU(cudaGetLastError());
-        frame_valid_ = is_root;
-        stats_.kernel_launches += (opts_.shard_mode == PATHS_SHARD_TILES) ? 1 : 0;
-        return wait ? sync() : PATHS_OK;
+        return PATHS_OK;
     }
 
     paths_status device_sums(void **ptr, size_t *n, int32_t *elem_bytes) override {

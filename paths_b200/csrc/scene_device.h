@@ -54,6 +54,10 @@ struct RendererBase {
     // renderer's rank; owned = destroy it with the renderer
     virtual paths_status attach_comm(void *comm, bool owned) = 0;
     virtual paths_status combine(int32_t root, bool wait) = 0;
+    // the two halves of combine() for a caller that issues several ranks' NCCL calls inside one ncclGroupStart / End (paths_group):
+    // NCCL defers grouped calls to the outermost GroupEnd, so what must run AFTER the transfer (the root's scatter) is launched after it
+    virtual paths_status combine_post(int32_t root) = 0;   // NCCL calls (and the kernels that feed them)
+    virtual paths_status combine_finish(int32_t root) = 0; // kernels that consume what was received
     virtual bool has_comm() const = 0;
     std::string err;
 };
