@@ -19,7 +19,11 @@ namespace paths {
 #define PATHS_LB_EXTEND 8
 #endif
 #ifndef PATHS_QBUF
-#define PATHS_QBUF 96u /* per-warp staging of surviving paths (ray pair + throughput, 3 vectors each) in the shade kernel */
+/* per-warp staging of surviving paths (ray pair + throughput, 3 vectors each) in the shade kernel.  Sweep on B200 (profiles/r02f_variants.txt,
+ * teapot / bunny M samples/s with two pass contexts): 96 -> 3718 / 2660, 64 -> 3773 / 2698, 48 -> 3400 / 2664: below 64 the queue-counter
+ * atomics come back (one per ~24 survivors), above it the shade grid's shared memory (18 KB per block) shrinks L1 for the closest-hit
+ * kernel of the other pass context that runs beside it */
+#define PATHS_QBUF 64u
 #endif
 #ifndef PATHS_LB_SHADE
 #define PATHS_LB_SHADE 5
