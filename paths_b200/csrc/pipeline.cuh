@@ -127,17 +127,30 @@ __global__ void __launch_bounds__(128) k_extend(DevScene sc, const typename Vec4
 // Primary rays of neighbouring slots are nearly parallel, so a warp's 32 rays walk the tree together: plain batches of 32
 // (no lane refill) are the faster schedule here (-2..3.5 % extend time), and generating the ray in the same kernel hides
 // raygen's 64 B/slot of HBM writes behind the traversal and saves reading the ray back (32 B/slot).
-template <typename R> // float only; a template so that both translation units may include this header
+// TILED (whole-frame passes): a warp takes an 8 x 4 pixel tile of one sample index instead of 32 consecutive pixels of a row -- the 32
+// primary rays stay closer together, so they agree on more of the tree (profiles/r02h_*: threads per instruction and kernel time).
+// The records still go to their own slots (bounce 0: position = slot), 8 consecutive 32-byte records per tile row.
+template <typename R, bool TILED> // float only; a template so that both translation units may include this header
 __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_camera_extend(DevScene sc, DevCamera cam, uint32_t k0, uint32_t k1, ShardInfo shard,
                                                                         uint32_t s_base, uint32_t n_slots, PathState<float4> ps, PassControl pc,
                                                                         uint32_t *cursor) {
     const uint32_t lane = threadIdx.x & 31u;
     if (blockIdx.x == 0 && threadIdx.x == 0) pc.qcount[0] = n_slots;
+    const uint32_t tiles_x = (cam.width + 7u) >> 3, tiles_y = (cam.height + 3u) >> 2, tiles = tiles_x * tiles_y;
+    const uint32_t n_work = TILED ? (n_slots / shard.n_local) * tiles * 32u : n_slots; // in units of lanes
     for (;;) {
         uint32_t base = warp_fetch(cursor);
-        if (base >= n_slots) break;
+        if (base >= n_work) break;
         uint32_t i = base + lane;
-        if (i < n_slots) {
+        bool valid = i < n_slots;
+        if (TILED) {
+            const uint32_t batch = base >> 5, k = batch / tiles, tile = batch - k * tiles;
+            const uint32_t ty = tile / tiles_x, tx = tile - ty * tiles_x;
+            const uint32_t x = (tx << 3) + (lane & 7u), y = (ty << 2) + (lane >> 3);
+            valid = x < cam.width && y < cam.height;
+            i = k * shard.n_local + y * cam.width + x;
+        }
+        if (valid) {
             uint32_t lp, k;
             shard.split(i, lp, k);
             uint32_t pixel = shard.pixels ? shard.pixels[lp] : lp;

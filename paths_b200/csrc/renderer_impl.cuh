@@ -44,6 +44,7 @@ template <typename R> class RendererImpl : public RendererBase {
     uint32_t samples_done_ = 0; // global samples per pixel issued so far (all ranks together)
     TraceConfig tc_; // which traversal kernels this scene runs on (shared with the per-ray seam, renderer.cuh)
     int grid_shade_ = 0, grid_stream_ = 0, shade_variant_ = 1;
+    bool camera_tiles_ = true;
     // device buffers
     R4 *sums_ = nullptr;
     // frame combine (NCCL): the communicator of this rank, the combined estimator on the root, tile-shard staging
@@ -246,6 +247,7 @@ template <typename R> class RendererImpl : public RendererBase {
         }
 #ifdef PATHS_DEV_SWITCHES
         if (const char *v = getenv("PATHS_SHADE_VARIANT")) shade_variant_ = atoi(v);
+        if (const char *v = getenv("PATHS_CAMERA_TILES")) camera_tiles_ = atoi(v) != 0;
 #endif
         int bps = 0;
         {
@@ -318,8 +320,13 @@ template <typename R> class RendererImpl : public RendererBase {
         for (uint32_t b = 0; b < nb; b++) {
             tic(1);
             if (b == 0 && fused_camera) {
-                if constexpr (!IsF64<R>::value)
-                    k_camera_extend<float><<<tc_.grid_camera, 128, 0, cs_>>>(sd_->view, cam_, k0, k1, shard, s_base, n_slots, ps_, pc_, pc_.work);
+                if constexpr (!IsF64<R>::value) {
+                    // whole frame in row-major order: warps take 8 x 4 pixel tiles; pixel tables (tile shards, column sweeps, preview): rows of 32
+                    if (camera_tiles_ && pixels == nullptr && n_local == npix_)
+                        k_camera_extend<float, true><<<tc_.grid_camera, 128, 0, cs_>>>(sd_->view, cam_, k0, k1, shard, s_base, n_slots, ps_, pc_, pc_.work);
+                    else
+                        k_camera_extend<float, false><<<tc_.grid_camera, 128, 0, cs_>>>(sd_->view, cam_, k0, k1, shard, s_base, n_slots, ps_, pc_, pc_.work);
+                }
             } else launch_extend(b);
             toc();
             stats_.n_extend_launches++;
