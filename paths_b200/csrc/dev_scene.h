@@ -118,7 +118,20 @@ struct ShardInfo {
     uint32_t n_local;         // pixels owned by this rank
     const uint32_t *pixels;   // local -> global pixel index, or NULL for identity
     uint32_t n_local_magic;   // floor(2^32 / n_local): slot / n_local without an integer division (see shard_split)
+    // Whole-frame passes (pixels == NULL) number their local pixels in 8 x 4 TILE order when the image size allows it (width % 8 == 0,
+    // height % 4 == 0; tiles_x = width / 8, else 0 = row-major): 32 consecutive slots are then an 8 x 4 block of pixels instead of a
+    // 32-pixel line, so the rays a warp generates, shades and re-emits start closer together and agree on more of the tree.  Results do
+    // not depend on the numbering (every pixel's samples are a function of (seed, pixel, sample) only).
+    uint32_t tiles_x, tiles_x_magic; // tiles_x_magic = floor(2^32 / tiles_x) + 1
 #if defined(__CUDACC__)
+    __device__ __forceinline__ uint32_t pixel_of(uint32_t lp) const {
+        if (pixels) return pixels[lp];
+        if (tiles_x == 0) return lp;
+        const uint32_t tile = lp >> 5, in = lp & 31u;
+        uint32_t ty = __umulhi(tile, tiles_x_magic); // tile / tiles_x: exact for tile < 2^32 / tiles_x with this magic (tiles are < 2^25)
+        uint32_t tx = tile - ty * tiles_x;
+        return ((ty << 2) + (in >> 3)) * (tiles_x << 3) + (tx << 3) + (in & 7u);
+    }
     // slot -> (local pixel, sample within the pass); the estimate __umulhi(slot, magic) is at most one too small
     __device__ __forceinline__ void split(uint32_t slot, uint32_t &lp, uint32_t &k) const {
         k = __umulhi(slot, n_local_magic);

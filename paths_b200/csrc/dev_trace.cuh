@@ -184,7 +184,7 @@ __device__ __forceinline__ bool triangle_hit_wt(float4 s0, float4 s1, float4 s2,
     float e1x = s1.x - s0.x, e1y = s1.y - s0.y, e1z = s1.z - s0.z, e2x = s2.x - s0.x, e2y = s2.y - s0.y, e2z = s2.z - s0.z;
     float nx = e1y * e2z - e1z * e2y, ny = e1z * e2x - e1x * e2z, nz = e1x * e2y - e1y * e2x;
     float t = (nx * a0 + ny * a1 + nz * a2) / (nx * dx + ny * dy + nz * dz);
-    if (!(t >= 0.0f && t < tmax)) return false;
+    if (!(t >= 0.0f && t <= tmax)) return false; // t == tmax passes: the caller breaks exact ties by primitive id
     float inv = 1.0f / det;
     h.t = t;
     h.bx = U * inv;
@@ -193,6 +193,14 @@ __device__ __forceinline__ bool triangle_hit_wt(float4 s0, float4 s1, float4 s2,
 }
 
 // ------------------------------------------------------------------ production traversal
+// Closest hit with an ORDER-INDEPENDENT rule for exact ties: of two primitives hit at bit-equal distances the lower id wins.  The box
+// tests never cull a candidate at t == best (tf = min(far, best) * 1.0000004 >= best), so every production kernel -- plain batches,
+// two-wide lane refill, four-wide with parked leaves -- returns the same (prim, t) for the same ray whatever order it visits the tree
+// in (tests/test_gpu_production_rays.py asserts that bit for bit).  The reference takes the first hit in ITS visiting order
+// (src/bvh.rs:93-104), which the f64 instantiation reproduces; a visibility query (any hit) is unaffected.
+__device__ __forceinline__ bool closer(float t_new, uint32_t prim_new, float t_best, uint32_t prim_best) {
+    return t_new < t_best || (t_new == t_best && prim_new < prim_best);
+}
 struct HitF {
     uint32_t prim;
     float t, bx, by;
@@ -286,7 +294,7 @@ template <bool ANY> __device__ __forceinline__ HitF trace_fast(const DevScene &s
                     double t;
                     if (sphere_hit64(mk3(cx, cy, cz), rr, mk3((double)ox, (double)oy, (double)oz), mk3((double)dx, (double)dy, (double)dz), t)) {
                         float tf = (float)t;
-                        if (tf < best.t) {
+                        if (ANY ? tf < best.t : closer(tf, prim, best.t, best.prim)) {
                             best.t = tf;
                             best.prim = prim;
                             best.bx = best.by = 0.0f;
@@ -295,7 +303,7 @@ template <bool ANY> __device__ __forceinline__ HitF trace_fast(const DevScene &s
                     }
                 } else { // triangle: v0 | v1 | v2, tag
                     TriHit th;
-                    if (triangle_hit_wt(s0, s1, s2, frame, ox, oy, oz, dx, dy, dz, best.t, th)) {
+                    if (triangle_hit_wt(s0, s1, s2, frame, ox, oy, oz, dx, dy, dz, best.t, th) && (ANY ? th.t < best.t : closer(th.t, prim, best.t, best.prim))) {
                         best.t = th.t;
                         best.prim = prim;
                         best.bx = th.bx;
@@ -462,14 +470,14 @@ struct TravF {
                 double tt;
                 if (sphere_hit64(mk3(cx, cy, cz), rr, mk3((double)ox, (double)oy, (double)oz), mk3((double)dx, (double)dy, (double)dz), tt)) {
                     float tf = (float)tt;
-                    if (tf < t) {
+                    if (ANY ? tf < t : closer(tf, p, t, prim)) {
                         t = tf; prim = p; bx = by = 0.0f;
                         if (ANY) return true;
                     }
                 }
             } else {
                 TriHit th;
-                if (triangle_hit_wt(s0, s1, s2, frame, ox, oy, oz, dx, dy, dz, t, th)) {
+                if (triangle_hit_wt(s0, s1, s2, frame, ox, oy, oz, dx, dy, dz, t, th) && (ANY ? th.t < t : closer(th.t, p, t, prim))) {
                     t = th.t; prim = p; bx = th.bx; by = th.by;
                     if (ANY) return true;
                 }

@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(256) k_raygen(DevCamera cam, uint32_t k0, uint
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += stride) {
         uint32_t lp, k;
         shard.split(i, lp, k);
-        uint32_t pixel = shard.pixels ? shard.pixels[lp] : lp;
+        uint32_t pixel = shard.pixel_of(lp);
         V3<R> o, d;
         R w;
         pixel_sample_ray<R>(cam, k0, k1, pixel, s_base + k, o, d, w);
@@ -127,33 +127,20 @@ __global__ void __launch_bounds__(128) k_extend(DevScene sc, const typename Vec4
 // Primary rays of neighbouring slots are nearly parallel, so a warp's 32 rays walk the tree together: plain batches of 32
 // (no lane refill) are the faster schedule here (-2..3.5 % extend time), and generating the ray in the same kernel hides
 // raygen's 64 B/slot of HBM writes behind the traversal and saves reading the ray back (32 B/slot).
-// TILED (whole-frame passes): a warp takes an 8 x 4 pixel tile of one sample index instead of 32 consecutive pixels of a row -- the 32
-// primary rays stay closer together, so they agree on more of the tree (profiles/r02h_*: threads per instruction and kernel time).
-// The records still go to their own slots (bounce 0: position = slot), 8 consecutive 32-byte records per tile row.
-template <typename R, bool TILED> // float only; a template so that both translation units may include this header
+template <typename R> // float only; a template so that both translation units may include this header
 __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_camera_extend(DevScene sc, DevCamera cam, uint32_t k0, uint32_t k1, ShardInfo shard,
                                                                         uint32_t s_base, uint32_t n_slots, PathState<float4> ps, PassControl pc,
                                                                         uint32_t *cursor) {
     const uint32_t lane = threadIdx.x & 31u;
     if (blockIdx.x == 0 && threadIdx.x == 0) pc.qcount[0] = n_slots;
-    const uint32_t tiles_x = (cam.width + 7u) >> 3, tiles_y = (cam.height + 3u) >> 2, tiles = tiles_x * tiles_y;
-    const uint32_t n_work = TILED ? (n_slots / shard.n_local) * tiles * 32u : n_slots; // in units of lanes
     for (;;) {
         uint32_t base = warp_fetch(cursor);
-        if (base >= n_work) break;
+        if (base >= n_slots) break;
         uint32_t i = base + lane;
-        bool valid = i < n_slots;
-        if (TILED) {
-            const uint32_t batch = base >> 5, k = batch / tiles, tile = batch - k * tiles;
-            const uint32_t ty = tile / tiles_x, tx = tile - ty * tiles_x;
-            const uint32_t x = (tx << 3) + (lane & 7u), y = (ty << 2) + (lane >> 3);
-            valid = x < cam.width && y < cam.height;
-            i = k * shard.n_local + y * cam.width + x;
-        }
-        if (valid) {
+        if (i < n_slots) {
             uint32_t lp, k;
             shard.split(i, lp, k);
-            uint32_t pixel = shard.pixels ? shard.pixels[lp] : lp;
+            uint32_t pixel = shard.pixel_of(lp); // whole-frame passes: 32 consecutive local pixels are an 8 x 4 tile (ShardInfo)
             V3<float> o, d;
             float w;
             pixel_sample_ray<float>(cam, k0, k1, pixel, s_base + k, o, d, w);
@@ -446,7 +433,7 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LI
             slot = real_to_bits(o4.w);
             uint32_t lp, k;
             shard.split(slot, lp, k);
-            uint32_t pixel = shard.pixels ? shard.pixels[lp] : lp;
+            uint32_t pixel = shard.pixel_of(lp);
             shade_path<R, LIGHTS, EXT>(sc, ps, o4, d4, h4, thr, slot, pixel, s_base + k, k0, k1, max_bounces, ext, totals, out);
         }
         if (LIGHTS) { // shadow records: staged per warp like the survivors below, appended SBUF - 32 or more at a time
@@ -934,7 +921,7 @@ __global__ void __launch_bounds__(256) k_accumulate(PathState<typename Vec4T<R>:
     typedef typename Vec4T<R>::type R4;
     uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t lp = blockIdx.x * blockDim.x + threadIdx.x; lp < shard.n_local; lp += stride) {
-        uint32_t pixel = shard.pixels ? shard.pixels[lp] : lp;
+        uint32_t pixel = shard.pixel_of(lp);
         R4 s = sums[pixel];
         for (uint32_t k = 0; k < spp_pass; k++) {
             R4 c = ld_rec(&ps.col[(size_t)k * shard.n_local + lp]);

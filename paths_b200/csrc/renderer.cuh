@@ -119,7 +119,7 @@ template <typename R> paths_status configure_trace(const SceneDevice *sd, TraceC
     } else {
         PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (k_extend_refill<1, 16, 8>), 128, 0));
         tc.grid_trace = tc.sm_count * std::max(bps, 1);
-        PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (k_camera_extend<float, true>), 128, 0));
+        PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_camera_extend<float>, 128, 0));
         tc.grid_camera = tc.sm_count * std::max(bps, 1);
         // four-wide kernels: stack of 3 * depth + 1 levels per thread in shared memory
         tc.smem4 = (size_t)(3 * sd->view.fast4_depth + 1) * 128 * sizeof(int32_t);

@@ -183,10 +183,7 @@ template <typename R> class RendererImpl : public RendererBase {
         // ---- shard: which pixels this rank owns
         if (opts_.shard_mode == PATHS_SHARD_TILES && world > 1) {
             std::vector<uint32_t> own;
-            uint32_t tiles_x = (W_ + 63) / 64;
-            for (uint32_t y = 0; y < H_; y++)
-                for (uint32_t x = 0; x < W_; x++)
-                    if (((y / 64) * tiles_x + (x / 64)) % world == opts_.rank) own.push_back(x + y * W_);
+            owned_pixels(W_, H_, opts_.rank, world, own);
             n_local_ = (uint32_t)own.size();
             if (alloc(&pixels_, own.size()) != PATHS_OK) return PATHS_ERR_CUDA;
             if (!own.empty()) PATHS_CU(cudaMemcpy(pixels_, own.data(), own.size() * 4, cudaMemcpyHostToDevice));
@@ -308,6 +305,14 @@ template <typename R> class RendererImpl : public RendererBase {
         shard.n_local = n_local;
         shard.pixels = pixels;
         shard.n_local_magic = n_local > 1 ? (uint32_t)((1ull << 32) / n_local) : 0xFFFFFFFFu;
+        // whole frame: local pixels numbered in 8 x 4 tile order when the size allows it (ShardInfo::pixel_of)
+        shard.tiles_x = 0;
+        shard.tiles_x_magic = 0;
+        if (camera_tiles_ && pixels == nullptr && n_local == npix_ && W_ % 8 == 0 && H_ % 4 == 0 && npix_ >= 32 &&
+            (uint64_t)(npix_ / 32) * (W_ / 8) < (1ull << 32)) { // the multiply-high division by tiles_x is exact below that
+            shard.tiles_x = W_ / 8;
+            shard.tiles_x_magic = (uint32_t)((1ull << 32) / shard.tiles_x) + 1u;
+        }
         const uint32_t nb = opts_.max_bounces + 1; // segments per path (trace.rs:13-16)
         PATHS_CU(cudaMemsetAsync(ctl_block_, 0, n_ctl_ * sizeof(uint32_t), cs_));
         bool fused_camera = false;
@@ -320,13 +325,8 @@ template <typename R> class RendererImpl : public RendererBase {
         for (uint32_t b = 0; b < nb; b++) {
             tic(1);
             if (b == 0 && fused_camera) {
-                if constexpr (!IsF64<R>::value) {
-                    // whole frame in row-major order: warps take 8 x 4 pixel tiles; pixel tables (tile shards, column sweeps, preview): rows of 32
-                    if (camera_tiles_ && pixels == nullptr && n_local == npix_)
-                        k_camera_extend<float, true><<<tc_.grid_camera, 128, 0, cs_>>>(sd_->view, cam_, k0, k1, shard, s_base, n_slots, ps_, pc_, pc_.work);
-                    else
-                        k_camera_extend<float, false><<<tc_.grid_camera, 128, 0, cs_>>>(sd_->view, cam_, k0, k1, shard, s_base, n_slots, ps_, pc_, pc_.work);
-                }
+                if constexpr (!IsF64<R>::value)
+                    k_camera_extend<float><<<tc_.grid_camera, 128, 0, cs_>>>(sd_->view, cam_, k0, k1, shard, s_base, n_slots, ps_, pc_, pc_.work);
             } else launch_extend(b);
             toc();
             stats_.n_extend_launches++;
@@ -492,12 +492,23 @@ template <typename R> class RendererImpl : public RendererBase {
         comm_owned_ = owned;
         return PATHS_OK;
     }
+    // The pixels of `rank` under tile sharding: 64 x 64 tiles dealt round-robin in row-major tile order (tile t -> rank t mod world).
+    // Listed tile by tile, and inside a tile in 8 x 4 blocks, so that 32 consecutive local pixels are a compact block of the image
+    // (same reason as ShardInfo::pixel_of).  Root and senders derive the same list, so the combine needs no exchange of indices.
     static void owned_pixels(uint32_t W, uint32_t H, uint32_t rank, uint32_t world, std::vector<uint32_t> &own) {
         own.clear();
-        uint32_t tiles_x = (W + 63) / 64;
-        for (uint32_t y = 0; y < H; y++)
-            for (uint32_t x = 0; x < W; x++)
-                if (((y / 64) * tiles_x + (x / 64)) % world == rank) own.push_back(x + y * W);
+        const uint32_t tiles_x = (W + 63) / 64, tiles_y = (H + 63) / 64;
+        for (uint32_t ty = 0; ty < tiles_y; ty++)
+            for (uint32_t tx = 0; tx < tiles_x; tx++) {
+                if ((ty * tiles_x + tx) % world != rank) continue;
+                for (uint32_t by = 0; by < 64; by += 4)
+                    for (uint32_t bx = 0; bx < 64; bx += 8)
+                        for (uint32_t iy = 0; iy < 4; iy++)
+                            for (uint32_t ix = 0; ix < 8; ix++) {
+                                const uint32_t x = tx * 64 + bx + ix, y = ty * 64 + by + iy;
+                                if (x < W && y < H) own.push_back(x + y * W);
+                            }
+            }
     }
     // Renderer::drain_result_queue -> Estimator::update_pixel (renderer.rs:93-105) across GPUs: partial estimators of all ranks are
     // combined on `root`, enqueued on the renderer's stream behind its passes.  Sample shards: ncclReduce(sum) of the {sum r, g, b, n}
