@@ -35,6 +35,30 @@ namespace paths {
 #define PATHS_LB_SHADE64 4
 #endif
 #define PATHS_FLAG_SPECULAR 0x100u
+#ifndef PATHS_SHADE_PARK
+#define PATHS_SHADE_PARK 1
+#endif
+// The production instantiations of the traversal kernels (tuned on B200, profiles/): <rounds between refill votes, idle lanes that
+// trigger a refill, inner nodes per round[, lanes that keep the inner phase going]>
+#ifndef PATHS_E2_MIN
+#define PATHS_E2_MIN 16
+#endif
+#ifndef PATHS_E2_KI
+#define PATHS_E2_KI 8
+#endif
+#ifndef PATHS_E4_MIN
+#define PATHS_E4_MIN 16
+#endif
+#ifndef PATHS_E4_KI
+#define PATHS_E4_KI 16
+#endif
+#ifndef PATHS_E4_INNER
+#define PATHS_E4_INNER 12
+#endif
+#define PATHS_K_EXTEND2 k_extend_refill<1, PATHS_E2_MIN, PATHS_E2_KI>
+#define PATHS_K_SHADOW2 k_shadow_refill<1, 16, 8>
+#define PATHS_K_EXTEND4 k_extend4s<1, PATHS_E4_MIN, PATHS_E4_KI, PATHS_E4_INNER>
+#define PATHS_K_SHADOW4 k_shadow4<4, 16, 2>
 
 template <typename R> struct IsF64 {
     static const bool value = false;
@@ -200,6 +224,20 @@ template <typename R> struct ShadeOut {
     uint32_t next_flags;
 };
 
+// A ray that left the scene: the sky's radiance along it, weighted by the path's throughput, goes to the path's radiance record (trace.rs:20-23)
+template <typename R, bool EXT>
+__device__ __forceinline__ void shade_miss(const DevScene &sc, PathState<typename Vec4T<R>::type> &ps, V3<R> rd, V3<R> throughput, bool last_specular,
+                                           uint32_t slot, uint32_t ext) {
+    typedef typename Vec4T<R>::type R4;
+    // with environment NEE the sky is accounted for at the previous vertex unless that bounce was specular (same rule
+    // the reference applies to lights, trace.rs:31-41)
+    if (EXT && (ext & PATHS_EXT_ENV_NEE) && sc.sky_type == 2 && !last_specular) return;
+    R4 c4 = ps.col[slot]; // the radiance record is only touched by the branches that add light
+    V3<R> colour = mk3<R>(c4.x, c4.y, c4.z);
+    colour = colour + throughput * sky_light<R>(sc, neg(rd));
+    ps.col[slot] = mk4(colour.x, colour.y, colour.z, c4.w);
+}
+
 // LIGHTS: the scene has lights (next-event estimation is compiled in); EXT: any estimator extension is on.  The common kernels --
 // no extensions, with or without lights -- carry none of the other code and keep their registers for occupancy.
 // o4 = {origin, slot}, d4 = {direction, flags}, h4 = hit record of this segment, throughput = the path's weight so far.
@@ -220,13 +258,7 @@ __device__ __forceinline__ void shade_path(const DevScene &sc, PathState<typenam
     const bool env_nee = EXT && (ext & PATHS_EXT_ENV_NEE) && sc.sky_type == 2;
 
     if (prim == 0xFFFFFFFFu) { // trace.rs:20-23
-        // with environment NEE the sky is accounted for at the previous vertex unless that bounce was specular (same rule
-        // the reference applies to lights, trace.rs:31-41)
-        if (env_nee && !last_specular) return;
-        R4 c4 = ps.col[slot]; // the radiance record is only touched by the branches that add light
-        V3<R> colour = mk3<R>(c4.x, c4.y, c4.z);
-        colour = colour + throughput * sky_light<R>(sc, neg(rd));
-        ps.col[slot] = mk4(colour.x, colour.y, colour.z, c4.w);
+        shade_miss<R, EXT>(sc, ps, rd, throughput, last_specular, slot, ext);
         return;
     }
     // ---- Collision (geom.rs:59-70) + Scene::find_intersection post-processing (scene.rs:172-197)
@@ -404,6 +436,87 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LI
     uint32_t sfill = 0; // warp-uniform
     const uint32_t warp_stride = gridDim.x * (blockDim.x >> 5) * 32u;
     uint32_t static_base = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 32u;
+#if PATHS_SHADE_PARK
+    __shared__ uint32_t park_all[4][64];
+    uint32_t *park = park_all[threadIdx.x >> 5];
+    uint32_t npark = 0; // warp-uniform
+#endif
+    // one group of up to 32 queue entries: shading, then warp-level staging of shadow records and survivors
+    auto shade_batch = [&](bool valid, uint32_t i) {
+            ShadeOut<R> out;
+            out.alive = out.shadow = out.shadow2 = false;
+            uint32_t slot = 0;
+            if (valid) {
+                R4 o4 = rin[2 * (size_t)i], d4 = rin[2 * (size_t)i + 1], h4 = ps.hit[i];
+                V3<R> thr = mk3<R>(R(1), R(1), R(1));
+                if (!first) {
+                    R4 t4 = tin[i];
+                    thr = mk3<R>(t4.x, t4.y, t4.z);
+                }
+                slot = real_to_bits(o4.w);
+                uint32_t lp, k;
+                shard.split(slot, lp, k);
+                uint32_t pixel = shard.pixel_of(lp);
+                shade_path<R, LIGHTS, EXT>(sc, ps, o4, d4, h4, thr, slot, pixel, s_base + k, k0, k1, max_bounces, ext, totals, out);
+            }
+            if (LIGHTS) { // shadow records: staged per warp like the survivors below, appended SBUF - 32 or more at a time
+                const unsigned m = __ballot_sync(PATHS_FULL_MASK, out.shadow);
+                if (out.shadow) {
+                    const uint32_t k = sfill + __popc(m & ((1u << lane) - 1u));
+                    sbuf[k] = mk4(out.sh_o.x, out.sh_o.y, out.sh_o.z, bits_to_real(out.light, R(0)));
+                    sbuf[SBUF + k] = mk4(out.sh_d.x, out.sh_d.y, out.sh_d.z, bits_to_real(slot, R(0)));
+                    sbuf[2 * SBUF + k] = mk4(out.sh_c.x, out.sh_c.y, out.sh_c.z, R(0));
+                }
+                sfill += __popc(m);
+                if (sfill > SBUF - 32u) {
+                    __syncwarp();
+                    uint32_t sbase = 0;
+                    if (lane == 0) sbase = atomicAdd(shadow_count, sfill);
+                    sbase = __shfl_sync(PATHS_FULL_MASK, sbase, 0);
+                    PATHS_DASSERT(sbase + sfill <= env_base);
+                    for (uint32_t k = lane; k < sfill; k += 32u) {
+                        ps.sh_o[sbase + k] = sbuf[k];
+                        ps.sh_d[sbase + k] = sbuf[SBUF + k];
+                        ps.sh_c[sbase + k] = sbuf[2 * SBUF + k];
+                    }
+                    sfill = 0;
+                    __syncwarp();
+                }
+            }
+            if (EXT && (ext & PATHS_EXT_ENV_NEE)) { // warp-uniform
+                // environment records go to the second half of the shadow arrays with a counter of their own; a launch of its own resolves
+                // them after the light records (two records of one slot in one launch would race on the slot's radiance record)
+                uint32_t epos = env_base + warp_append(env_count, out.shadow2);
+                if (out.shadow2) {
+                    ps.sh_o[epos] = mk4(out.sh_o.x, out.sh_o.y, out.sh_o.z, bits_to_real(PATHS_LIGHT_ENV, R(0)));
+                    ps.sh_d[epos] = mk4(out.sh2_d.x, out.sh2_d.y, out.sh2_d.z, bits_to_real(slot, R(0)));
+                    ps.sh_c[epos] = mk4(out.sh2_c.x, out.sh2_c.y, out.sh2_c.z, R(0));
+                }
+            }
+            // surviving paths: their next segment is gathered per warp in shared memory and appended to the next bounce's dense arrays
+            // QB - 32 or more at a time (one counter atomic and full-line stores per flush instead of one atomic per batch)
+            {
+                const unsigned m = __ballot_sync(PATHS_FULL_MASK, out.alive);
+                if (out.alive) {
+                    const uint32_t k = fill + __popc(m & ((1u << lane) - 1u));
+                    qbuf[2 * k] = mk4(out.next_o.x, out.next_o.y, out.next_o.z, bits_to_real(slot, R(0)));
+                    qbuf[2 * k + 1] = mk4(out.next_d.x, out.next_d.y, out.next_d.z, bits_to_real(out.next_flags, R(0)));
+                    qbuf[2 * QB + k] = mk4(out.next_thr.x, out.next_thr.y, out.next_thr.z, R(0));
+                }
+                fill += __popc(m);
+                if (fill > QB - 32u) {
+                    __syncwarp();
+                    uint32_t qbase = 0;
+                    if (lane == 0) qbase = atomicAdd(next_count, fill);
+                    qbase = __shfl_sync(PATHS_FULL_MASK, qbase, 0);
+                    PATHS_DASSERT(qbase + fill <= env_base);
+                    for (uint32_t k = lane; k < 2u * fill; k += 32u) rout[2 * (size_t)qbase + k] = qbuf[k];
+                    for (uint32_t k = lane; k < fill; k += 32u) tout[qbase + k] = qbuf[2 * QB + k];
+                    fill = 0;
+                    __syncwarp();
+                }
+            }
+    };
     for (;;) {
         uint32_t base;
         if (cursor) base = warp_fetch(cursor);
@@ -420,80 +533,50 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LI
         }
         if (base >= count) break;
         uint32_t i = base + lane;
-        ShadeOut<R> out;
-        out.alive = out.shadow = out.shadow2 = false;
-        uint32_t slot = 0;
-        if (i < count) {
-            R4 o4 = rin[2 * (size_t)i], d4 = rin[2 * (size_t)i + 1], h4 = ps.hit[i];
-            V3<R> thr = mk3<R>(R(1), R(1), R(1));
-            if (!first) {
-                R4 t4 = tin[i];
-                thr = mk3<R>(t4.x, t4.y, t4.z);
-            }
-            slot = real_to_bits(o4.w);
-            uint32_t lp, k;
-            shard.split(slot, lp, k);
-            uint32_t pixel = shard.pixel_of(lp);
-            shade_path<R, LIGHTS, EXT>(sc, ps, o4, d4, h4, thr, slot, pixel, s_base + k, k0, k1, max_bounces, ext, totals, out);
-        }
-        if (LIGHTS) { // shadow records: staged per warp like the survivors below, appended SBUF - 32 or more at a time
-            const unsigned m = __ballot_sync(PATHS_FULL_MASK, out.shadow);
-            if (out.shadow) {
-                const uint32_t k = sfill + __popc(m & ((1u << lane) - 1u));
-                sbuf[k] = mk4(out.sh_o.x, out.sh_o.y, out.sh_o.z, bits_to_real(out.light, R(0)));
-                sbuf[SBUF + k] = mk4(out.sh_d.x, out.sh_d.y, out.sh_d.z, bits_to_real(slot, R(0)));
-                sbuf[2 * SBUF + k] = mk4(out.sh_c.x, out.sh_c.y, out.sh_c.z, R(0));
-            }
-            sfill += __popc(m);
-            if (sfill > SBUF - 32u) {
-                __syncwarp();
-                uint32_t sbase = 0;
-                if (lane == 0) sbase = atomicAdd(shadow_count, sfill);
-                sbase = __shfl_sync(PATHS_FULL_MASK, sbase, 0);
-                PATHS_DASSERT(sbase + sfill <= env_base);
-                for (uint32_t k = lane; k < sfill; k += 32u) {
-                    ps.sh_o[sbase + k] = sbuf[k];
-                    ps.sh_d[sbase + k] = sbuf[SBUF + k];
-                    ps.sh_c[sbase + k] = sbuf[2 * SBUF + k];
+        const bool in_range = i < count;
+#if PATHS_SHADE_PARK
+        // Rays that left the scene are finished at once; hits are PARKED (their queue positions, per warp, in shared memory) and shaded 32
+        // at a time, so that the long material / sampling code runs with full warps (ncu on teapot bounce 1, where 45 % of the rays
+        // miss: 15 of 32 lanes per instruction before).  Records are dense and prefetched, so the parked gather costs no extra latency.
+        bool is_hit = false;
+        if (in_range) {
+            const R4 h4 = ps.hit[i];
+            if (real_to_bits(h4.x) == 0xFFFFFFFFu) {
+                const R4 d4 = rin[2 * (size_t)i + 1];
+                V3<R> thr = mk3<R>(R(1), R(1), R(1));
+                if (!first) {
+                    const R4 t4 = tin[i];
+                    thr = mk3<R>(t4.x, t4.y, t4.z);
                 }
-                sfill = 0;
-                __syncwarp();
-            }
+                const uint32_t mslot = first ? i : real_to_bits(rin[2 * (size_t)i].w);
+                shade_miss<R, EXT>(sc, ps, mk3<R>(d4.x, d4.y, d4.z), thr, (real_to_bits(d4.w) & PATHS_FLAG_SPECULAR) != 0, mslot, ext);
+            } else is_hit = true;
         }
-        if (EXT && (ext & PATHS_EXT_ENV_NEE)) { // warp-uniform
-            // environment records go to the second half of the shadow arrays with a counter of their own; a launch of its own resolves
-            // them after the light records (two records of one slot in one launch would race on the slot's radiance record)
-            uint32_t epos = env_base + warp_append(env_count, out.shadow2);
-            if (out.shadow2) {
-                ps.sh_o[epos] = mk4(out.sh_o.x, out.sh_o.y, out.sh_o.z, bits_to_real(PATHS_LIGHT_ENV, R(0)));
-                ps.sh_d[epos] = mk4(out.sh2_d.x, out.sh2_d.y, out.sh2_d.z, bits_to_real(slot, R(0)));
-                ps.sh_c[epos] = mk4(out.sh2_c.x, out.sh2_c.y, out.sh2_c.z, R(0));
-            }
-        }
-        // surviving paths: their next segment is gathered per warp in shared memory and appended to the next bounce's dense arrays
-        // QB - 32 or more at a time (one counter atomic and full-line stores per flush instead of one atomic per batch)
         {
-            const unsigned m = __ballot_sync(PATHS_FULL_MASK, out.alive);
-            if (out.alive) {
-                const uint32_t k = fill + __popc(m & ((1u << lane) - 1u));
-                qbuf[2 * k] = mk4(out.next_o.x, out.next_o.y, out.next_o.z, bits_to_real(slot, R(0)));
-                qbuf[2 * k + 1] = mk4(out.next_d.x, out.next_d.y, out.next_d.z, bits_to_real(out.next_flags, R(0)));
-                qbuf[2 * QB + k] = mk4(out.next_thr.x, out.next_thr.y, out.next_thr.z, R(0));
-            }
-            fill += __popc(m);
-            if (fill > QB - 32u) {
-                __syncwarp();
-                uint32_t qbase = 0;
-                if (lane == 0) qbase = atomicAdd(next_count, fill);
-                qbase = __shfl_sync(PATHS_FULL_MASK, qbase, 0);
-                PATHS_DASSERT(qbase + fill <= env_base);
-                for (uint32_t k = lane; k < 2u * fill; k += 32u) rout[2 * (size_t)qbase + k] = qbuf[k];
-                for (uint32_t k = lane; k < fill; k += 32u) tout[qbase + k] = qbuf[2 * QB + k];
-                fill = 0;
-                __syncwarp();
-            }
+            const unsigned pm = __ballot_sync(PATHS_FULL_MASK, is_hit);
+            if (is_hit) park[npark + __popc(pm & ((1u << lane) - 1u))] = i;
+            npark += __popc(pm);
         }
+        if (npark < 32u) continue;
+        __syncwarp();
+        i = park[lane];
+        const uint32_t left = npark - 32u; // < 32
+        __syncwarp();
+        const uint32_t moved = lane < left ? park[32u + lane] : 0u;
+        __syncwarp();
+        if (lane < left) park[lane] = moved;
+        npark = left;
+        shade_batch(true, i);
+#else
+        shade_batch(in_range, i);
+#endif
     }
+#if PATHS_SHADE_PARK
+    if (npark > 0) { // the last, partial group of parked hits
+        __syncwarp();
+        shade_batch(lane < npark, lane < npark ? park[lane] : 0u);
+    }
+#endif
     if (LIGHTS && sfill > 0) {
         __syncwarp();
         uint32_t sbase = 0;

@@ -117,7 +117,7 @@ template <typename R> paths_status configure_trace(const SceneDevice *sd, TraceC
         tc.variant = 0;
         tc.variant_b0 = 0;
     } else {
-        PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (k_extend_refill<1, 16, 8>), 128, 0));
+        PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (PATHS_K_EXTEND2), 128, 0));
         tc.grid_trace = tc.sm_count * std::max(bps, 1);
         PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_camera_extend<float>, 128, 0));
         tc.grid_camera = tc.sm_count * std::max(bps, 1);
@@ -127,9 +127,9 @@ template <typename R> paths_status configure_trace(const SceneDevice *sd, TraceC
             if (tc.variant == 16) tc.variant = 3; // pathological tree: the two-wide kernels keep their stack in local memory
             tc.smem4 = 0;
         } else {
-            PATHS_CU(cudaFuncSetAttribute(k_shadow4<4, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc.smem4));
-            PATHS_CU(cudaFuncSetAttribute(k_extend4s<1, 16, 16, 12>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc.smem4));
-            PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_extend4s<1, 16, 16, 12>, 128, tc.smem4));
+            PATHS_CU(cudaFuncSetAttribute(PATHS_K_SHADOW4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc.smem4));
+            PATHS_CU(cudaFuncSetAttribute(PATHS_K_EXTEND4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc.smem4));
+            PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, PATHS_K_EXTEND4, 128, tc.smem4));
             tc.grid4 = tc.sm_count * std::max(bps, 1);
         }
     }
@@ -287,8 +287,8 @@ paths_status trace_closest_impl(const SceneDevice *sd, const double *o, const do
             const uint32_t host_ctl[2] = {(uint32_t)n, 0u}; // queue length, fetch cursor
             PATHS_CU(cudaMemcpy(ctl, host_ctl, sizeof(host_ctl), cudaMemcpyHostToDevice));
             k_stage_rays<R4><<<blocks, 128>>>(d_o, d_d, (uint32_t)n, ps.ray[0]);
-            if (variant == 16) k_extend4s<1, 16, 16, 12><<<tc.grid4, 128, tc.smem4>>>(sd->view, ps.ray[0], ps.hit, ctl, ctl + 1);
-            else if (variant == 3) k_extend_refill<1, 16, 8><<<tc.grid_trace, 128>>>(sd->view, ps.ray[0], ps.hit, ctl, ctl + 1);
+            if (variant == 16) PATHS_K_EXTEND4<<<tc.grid4, 128, tc.smem4>>>(sd->view, ps.ray[0], ps.hit, ctl, ctl + 1);
+            else if (variant == 3) PATHS_K_EXTEND2<<<tc.grid_trace, 128>>>(sd->view, ps.ray[0], ps.hit, ctl, ctl + 1);
             else k_extend<R, false><<<tc.grid_trace, 128>>>(sd->view, ps.ray[0], ps.hit, ctl, ctl + 1);
             k_unstage_hits<R4><<<blocks, 128>>>(ps.hit, sd->view, (uint32_t)n, d_p, d_t, d_b);
             staged = true;
@@ -353,10 +353,10 @@ paths_status trace_occluded_impl(const SceneDevice *sd, const double *o, const d
     bool launched = false;
     if constexpr (!IsF64<R>::value) {
         if (variant == 16) {
-            k_shadow4<4, 16, 2><<<tc.grid4, 128, tc.smem4>>>(sd->view, ps, ctl, ctl + 1, totals);
+            PATHS_K_SHADOW4<<<tc.grid4, 128, tc.smem4>>>(sd->view, ps, ctl, ctl + 1, totals);
             launched = true;
         } else if (variant == 3) {
-            k_shadow_refill<1, 16, 8><<<tc.grid_trace, 128>>>(sd->view, ps, ctl, ctl + 1, totals);
+            PATHS_K_SHADOW2<<<tc.grid_trace, 128>>>(sd->view, ps, ctl, ctl + 1, totals);
             launched = true;
         }
     }

@@ -268,9 +268,9 @@ template <typename R> class RendererImpl : public RendererBase {
 #ifdef PATHS_EXTEND2_SPEC
             case 3: k_extend2s<1, 16, PATHS_EXTEND2_KI, PATHS_EXTEND2_SPEC><<<tc_.grid_trace, 128, 0, cs_>>>(sd_->view, q, ps_.hit, cnt, cur); return;
 #else
-            case 3: k_extend_refill<1, 16, 8><<<tc_.grid_trace, 128, 0, cs_>>>(sd_->view, q, ps_.hit, cnt, cur); return;
+            case 3: PATHS_K_EXTEND2<<<tc_.grid_trace, 128, 0, cs_>>>(sd_->view, q, ps_.hit, cnt, cur); return;
 #endif
-            case 16: k_extend4s<1, 16, 16, 12><<<tc_.grid4, 128, tc_.smem4, cs_>>>(sd_->view, q, ps_.hit, cnt, cur); return;
+            case 16: PATHS_K_EXTEND4<<<tc_.grid4, 128, tc_.smem4, cs_>>>(sd_->view, q, ps_.hit, cnt, cur); return;
             default: break;
             }
         }
@@ -281,11 +281,11 @@ template <typename R> class RendererImpl : public RendererBase {
     void launch_shadow(const PathState<R4> &ps, const uint32_t *count, uint32_t *cursor) {
         if constexpr (!IsF64<R>::value) {
             if (tc_.variant == 16) {
-                k_shadow4<4, 16, 2><<<tc_.grid4, 128, tc_.smem4, cs_>>>(sd_->view, ps, count, cursor, pc_.totals);
+                PATHS_K_SHADOW4<<<tc_.grid4, 128, tc_.smem4, cs_>>>(sd_->view, ps, count, cursor, pc_.totals);
                 return;
             }
             if (tc_.variant != 0) {
-                k_shadow_refill<1, 16, 8><<<tc_.grid_trace, 128, 0, cs_>>>(sd_->view, ps, count, cursor, pc_.totals);
+                PATHS_K_SHADOW2<<<tc_.grid_trace, 128, 0, cs_>>>(sd_->view, ps, count, cursor, pc_.totals);
                 return;
             }
         }

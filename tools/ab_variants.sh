@@ -1,7 +1,7 @@
 #!/bin/bash
 # tools/ab_variants.sh "<variant dirs>" "<scenes>" [spp] -- same-box comparison of library builds kept under ab/ (see tools/build_variant.sh); "." = this tree
 variants=$1; scenes=${2:-"teapot"}; spp=${3:-64}
-for round in 1 2; do
+for round in $(seq 1 ${ROUNDS:-2}); do
   for s in $scenes; do
     for which in $variants; do
       d=$which; [ "$which" != "." ] && d=ab/$which
