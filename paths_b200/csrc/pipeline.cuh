@@ -436,11 +436,12 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LI
     uint32_t sfill = 0; // warp-uniform
     const uint32_t warp_stride = gridDim.x * (blockDim.x >> 5) * 32u;
     uint32_t static_base = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 32u;
-#if PATHS_SHADE_PARK
-    __shared__ uint32_t park_all[4][64];
+    // Parking pays where shading a hit is long (next-event estimation, extensions): bunny shade -12 %; the plain kernel (no lights, no
+    // extensions) is too light for it: teapot shade +2 %, environment.yml +30 % (profiles/r02l_sweep.txt) -- it keeps plain batches.
+    constexpr bool PARK = PATHS_SHADE_PARK && (LIGHTS || EXT);
+    __shared__ uint32_t park_all[4][PARK ? 64 : 1];
     uint32_t *park = park_all[threadIdx.x >> 5];
     uint32_t npark = 0; // warp-uniform
-#endif
     // one group of up to 32 queue entries: shading, then warp-level staging of shadow records and survivors
     auto shade_batch = [&](bool valid, uint32_t i) {
             ShadeOut<R> out;
@@ -534,7 +535,7 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LI
         if (base >= count) break;
         uint32_t i = base + lane;
         const bool in_range = i < count;
-#if PATHS_SHADE_PARK
+        if constexpr (PARK) {
         // Rays that left the scene are finished at once; hits are PARKED (their queue positions, per warp, in shared memory) and shaded 32
         // at a time, so that the long material / sampling code runs with full warps (ncu on teapot bounce 1, where 45 % of the rays
         // miss: 15 of 32 lanes per instruction before).  Records are dense and prefetched, so the parked gather costs no extra latency.
@@ -567,16 +568,12 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LI
         if (lane < left) park[lane] = moved;
         npark = left;
         shade_batch(true, i);
-#else
-        shade_batch(in_range, i);
-#endif
+        } else shade_batch(in_range, i);
     }
-#if PATHS_SHADE_PARK
-    if (npark > 0) { // the last, partial group of parked hits
+    if (PARK && npark > 0) { // the last, partial group of parked hits
         __syncwarp();
         shade_batch(lane < npark, lane < npark ? park[lane] : 0u);
     }
-#endif
     if (LIGHTS && sfill > 0) {
         __syncwarp();
         uint32_t sbase = 0;
