@@ -426,11 +426,11 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LI
     // parameters so that they are constant-bank operands, not registers (and never a dynamic index into the parameter block).
     // cursor == nullptr: batches of 32 entries are dealt to the warps of the grid round-robin (shading cost per entry is
     // uniform enough) -- no fetch atomic on the critical path; the next batch's records are prefetched into L2 meanwhile
-    constexpr uint32_t QB = IsF64<R>::value ? 48u : PATHS_QBUF; // survivors staged per warp: {origin | slot, direction | flags} pairs, then throughputs
+    constexpr uint32_t QB = IsF64<R>::value ? 56u : PATHS_QBUF; // survivors staged per warp: {origin | slot, direction | flags} pairs, then throughputs
     __shared__ R4 qbuf_all[4][3 * QB];
     R4 *qbuf = qbuf_all[threadIdx.x >> 5];
     uint32_t fill = 0; // warp-uniform
-    constexpr uint32_t SBUF = LIGHTS ? (IsF64<R>::value ? 64u : 96u) : 1u; // shadow records staged per warp (origin | direction | contribution)
+    constexpr uint32_t SBUF = LIGHTS ? (IsF64<R>::value ? 56u : 96u) : 1u; // f64: 2 x 21.5 KB of static shared memory per block (48 KB limit) // shadow records staged per warp (origin | direction | contribution)
     __shared__ R4 sbuf_all[4][3 * SBUF];
     R4 *sbuf = sbuf_all[threadIdx.x >> 5];
     uint32_t sfill = 0; // warp-uniform
