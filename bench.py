@@ -509,7 +509,7 @@ def run_ours(args, rank, world, local_rank):
                     "what": f"set_camera (new epoch) + render + RGB24 frame to pinned host memory through the C ABI on {world} GPU(s)"
                             + (", combine on rank 0 inside the library (NCCL) inside the timed region" if world > 1 else "")},
             "gpu_launches": int(tot_launch),
-            "combine": None if world == 1 else ("paths_renderer_combine inside libpaths_b200.so: " + ("ncclSend/ncclRecv of owned 64x64 tiles" if args.shard == "tiles" else "ncclReduce(sum) of the float4 estimator") + f", {pb.nccl_info()}"),
+            "combine": None if world == 1 else ("paths_renderer_combine inside libpaths_b200.so: " + ("ncclSend/ncclRecv of owned 32x32 tiles" if args.shard == "tiles" else "ncclReduce(sum) of the float4 estimator") + f", {pb.nccl_info()}"),
             "roofline": roof,
             "cpu_baseline": cpu,
             "cpu_baseline_t4": cpu_t4,
@@ -536,7 +536,7 @@ def main():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--spp-frame", type=int, default=256, help="strong scaling: samples per pixel per step in total (SURVEY C2/C4: 256)")
     ap.add_argument("--shard", default="samples", choices=["samples", "tiles"],
-                    help="N > 1: each GPU renders a sample range of every pixel (default) or all samples of its 64x64 tiles")
+                    help="N > 1: each GPU renders a sample range of every pixel (default) or all samples of its 32x32 tiles")
     ap.add_argument("--precision", type=int, default=0, choices=[0, 32, 48, 64])
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--also", default="dragon,environment:tiles",

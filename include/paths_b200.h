@@ -281,7 +281,7 @@ paths_status paths_renderer_reset(paths_renderer *r);
  * of all ranks of a frame are combined on `root` over NCCL (NVLink / NVSwitch), enqueued on the renderer's stream behind its passes.
  *   sample shards (PATHS_SHARD_SAMPLES): ncclReduce(sum) of the {sum r, sum g, sum b, count} buffers -- equal to one GPU up to the
  *     order of the f32 additions;
- *   tile shards (PATHS_SHARD_TILES): ranks own disjoint 64x64 tiles, so each packs its pixels and ncclSend's them, the root receives all
+ *   tile shards (PATHS_SHARD_TILES): ranks own disjoint 32x32 tiles, so each packs its pixels and ncclSend's them, the root receives all
  *     of them in one NCCL group and scatters them -- bit-identical to one GPU, 1/world of the bytes of a full-frame reduce.
  * After a combine the root's image / estimator reads (image_f32, image_rgb24, get_sums) show the combined frame until the next sample is
  * rendered; each rank's own estimator is left untouched, so render -> combine -> render -> combine accumulates correctly.

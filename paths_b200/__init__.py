@@ -219,7 +219,7 @@ class Renderer:
     """Renderer (src/renderer.rs:33-141) on one GPU.
 
     `num_workers` of the reference has no meaning here; `rank` / `world` / `shard_mode` select this process's share of the
-    frame (samples or 64x64 tiles) when several GPUs render one image.
+    frame (samples or 32x32 tiles) when several GPUs render one image.
     """
 
     def __init__(self, camera, scene, device=0, precision=PRECISION_AUTO, seed=1, rank=0, world=1, shard_mode=SHARD_SAMPLES,

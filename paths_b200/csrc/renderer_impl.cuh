@@ -4,6 +4,9 @@
 
 #include "renderer.cuh"
 
+#ifndef PATHS_SHARD_TILE
+#define PATHS_SHARD_TILE 32u /* edge of the square image tiles dealt to the ranks under PATHS_SHARD_TILES */
+#endif
 #ifndef PATHS_EXTEND2_KI
 #define PATHS_EXTEND2_KI 12
 #endif
@@ -492,20 +495,22 @@ template <typename R> class RendererImpl : public RendererBase {
         comm_owned_ = owned;
         return PATHS_OK;
     }
-    // The pixels of `rank` under tile sharding: 64 x 64 tiles dealt round-robin in row-major tile order (tile t -> rank t mod world).
-    // Listed tile by tile, and inside a tile in 8 x 4 blocks, so that 32 consecutive local pixels are a compact block of the image
-    // (same reason as ShardInfo::pixel_of).  Root and senders derive the same list, so the combine needs no exchange of indices.
+    // The pixels of `rank` under tile sharding: PATHS_SHARD_TILE x PATHS_SHARD_TILE tiles (32: at 64 the 64 tiles a rank of 8 gets at
+    // 1080p left its time 6.5 % above the mean on environment.yml -- sky tiles against mesh tiles; profiles/r02n_bench_n8_environment_tiles.json)
+    // dealt round-robin in row-major tile order (tile t -> rank t mod world).  Listed tile by tile, and inside a tile in 8 x 4 blocks, so
+    // that 32 consecutive local pixels are a compact block of the image (same reason as ShardInfo::pixel_of).  Root and senders derive the
+    // same list, so the combine needs no exchange of indices.
     static void owned_pixels(uint32_t W, uint32_t H, uint32_t rank, uint32_t world, std::vector<uint32_t> &own) {
         own.clear();
-        const uint32_t tiles_x = (W + 63) / 64, tiles_y = (H + 63) / 64;
+        const uint32_t T = PATHS_SHARD_TILE, tiles_x = (W + T - 1) / T, tiles_y = (H + T - 1) / T;
         for (uint32_t ty = 0; ty < tiles_y; ty++)
             for (uint32_t tx = 0; tx < tiles_x; tx++) {
                 if ((ty * tiles_x + tx) % world != rank) continue;
-                for (uint32_t by = 0; by < 64; by += 4)
-                    for (uint32_t bx = 0; bx < 64; bx += 8)
+                for (uint32_t by = 0; by < T; by += 4)
+                    for (uint32_t bx = 0; bx < T; bx += 8)
                         for (uint32_t iy = 0; iy < 4; iy++)
                             for (uint32_t ix = 0; ix < 8; ix++) {
-                                const uint32_t x = tx * 64 + bx + ix, y = ty * 64 + by + iy;
+                                const uint32_t x = tx * T + bx + ix, y = ty * T + by + iy;
                                 if (x < W && y < H) own.push_back(x + y * W);
                             }
             }

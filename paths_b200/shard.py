@@ -1,12 +1,12 @@
 """Host-side sharding rules of the multi-GPU path (mirrors RendererImpl::init / render in csrc/renderer_impl.cuh).
 
-Frames shard by sample range or by 64x64 image tile; the only exchange is one sum-reduce of the
+Frames shard by sample range or by 32x32 image tile; the only exchange is one sum-reduce of the
 {sum r, sum g, sum b, count} buffer per frame.  These helpers are what bench.py and multi-process drivers use to
 decide who renders what and to combine partial estimator buffers through torch.distributed (NCCL on GPUs, gloo in tests).
 """
 from __future__ import annotations
 
-TILE = 64
+TILE = 32  # PATHS_SHARD_TILE in csrc/renderer_impl.cuh
 
 
 def sample_slice(done, spp, rank, world):

@@ -68,7 +68,7 @@ def test_combine_without_a_communicator_is_refused(pb):
 @pytest.mark.parametrize("shard", ["tiles", "samples"])
 def test_group_frame_equals_one_gpu(pb, n, shard):
     need(pb, n)
-    sc = pb.Scene.load("scenes/bunny.yml", width=640, height=360)  # 60 tiles of 64x64, partial ones at the right and bottom edges
+    sc = pb.Scene.load("scenes/bunny.yml", width=640, height=360)  # 240 tiles of 32x32, partial ones at the bottom edge
     spp = 16
     ref, rgb = one_gpu(pb, sc, spp)
     g = pb.RendererGroup(sc.camera, sc, n, precision=32, seed=5, shard_mode=pb.SHARD_TILES if shard == "tiles" else pb.SHARD_SAMPLES)

@@ -74,6 +74,6 @@ def test_sample_slices_partition_the_range():
                 lo, hi = shard.sample_slice(10, spp, r, world)
                 seen += list(range(lo, hi))
             assert seen == list(range(10, 10 + spp))
-    tiles = {shard.tile_owner(x, y, 200, 3) for x in range(0, 200, 64) for y in range(0, 136, 64)}
+    tiles = {shard.tile_owner(x, y, 200, 3) for x in range(0, 200, 32) for y in range(0, 136, 32)}
     assert tiles == {0, 1, 2}
     assert sum(len(shard.owned_pixels(200, 136, r, 3)) for r in range(3)) == 200 * 136
