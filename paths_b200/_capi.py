@@ -9,8 +9,11 @@ import ctypes as C
 import subprocess
 from pathlib import Path
 
+import os
+
 _PKG = Path(__file__).resolve().parent
-LIB_PATH = _PKG / "lib" / "libpaths_b200.so"
+# PATHS_B200_LIB points the mirror at another build of the same ABI (the debug-assert build, a variant under ab/); never at a fallback
+LIB_PATH = Path(os.environ["PATHS_B200_LIB"]).resolve() if os.environ.get("PATHS_B200_LIB") else _PKG / "lib" / "libpaths_b200.so"
 
 OK, ERR_INVALID_ARG, ERR_IO, ERR_PARSE, ERR_CUDA, ERR_UNSUPPORTED, ERR_INTERNAL, ERR_NCCL = range(8)
 COMM_ID_BYTES = 128
