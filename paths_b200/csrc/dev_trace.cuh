@@ -550,4 +550,22 @@ struct TravF4 : TravF {
     __device__ __forceinline__ int32_t pop4(const int32_t *sstack, uint32_t stride) { return sp > 0 ? sstack[(--sp) * stride] : PATHS_TRAV_DONE; }
 };
 
+
+// plain per-lane closest hit over the four-wide nodes (camera segment of large scenes, and the per-ray seam that tests it)
+__device__ __forceinline__ HitF trace_plain4(const DevScene &sc, float ox, float oy, float oz, float dx, float dy, float dz, int32_t *sstack,
+                                             uint32_t stride) {
+    TravF4 tv;
+    tv.init(ox, oy, oz, dx, dy, dz, __int_as_float(0x7f800000), sc.fast4_root);
+    while (tv.node != PATHS_TRAV_DONE) {
+        if (tv.node >= 0) tv.inner4(sc.fast4_nodes, sstack, stride);
+        else {
+            tv.leaf_test<false>(sc.fast_leaves, tv.node, 0xFFFFFFFFu);
+            tv.node = tv.pop4(sstack, stride);
+        }
+    }
+    HitF h;
+    h.prim = tv.prim; h.t = tv.t; h.bx = tv.bx; h.by = tv.by;
+    return h;
+}
+
 } // namespace paths

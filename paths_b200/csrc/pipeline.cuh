@@ -151,10 +151,13 @@ __global__ void __launch_bounds__(128) k_extend(DevScene sc, const typename Vec4
 // Primary rays of neighbouring slots are nearly parallel, so a warp's 32 rays walk the tree together: plain batches of 32
 // (no lane refill) are the faster schedule here (-2..3.5 % extend time), and generating the ray in the same kernel hides
 // raygen's 64 B/slot of HBM writes behind the traversal and saves reading the ray back (32 B/slot).
-template <typename R> // float only; a template so that both translation units may include this header
+// WIDE4 (scenes above 64k primitives): the closest hit walks the four-wide nodes (stack in shared memory) in a plain per-lane loop -- fewer
+// dependent node fetches per ray, one 128-byte line per step.  Results are the same either way (closest hit, ties to the lower id).
+template <typename R, bool WIDE4> // float only; a template so that both translation units may include this header
 __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_camera_extend(DevScene sc, DevCamera cam, uint32_t k0, uint32_t k1, ShardInfo shard,
                                                                         uint32_t s_base, uint32_t n_slots, PathState<float4> ps, PassControl pc,
                                                                         uint32_t *cursor) {
+    extern __shared__ int32_t smem_stack[];
     const uint32_t lane = threadIdx.x & 31u;
     if (blockIdx.x == 0 && threadIdx.x == 0) pc.qcount[0] = n_slots;
     for (;;) {
@@ -172,7 +175,8 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_camera_extend(DevScene
             st_rec(&ps.ray[0][2 * i], make_float4(o.x, o.y, o.z, __uint_as_float(i)));
             st_rec(&ps.ray[0][2 * i + 1], make_float4(d.x, d.y, d.z, __uint_as_float(PATHS_FLAG_SPECULAR)));
             st_rec(&ps.col[i], make_float4(0.0f, 0.0f, 0.0f, w));
-            HitF h = trace_fast<false>(sc, o.x, o.y, o.z, d.x, d.y, d.z, __int_as_float(0x7f800000), 0xFFFFFFFFu);
+            HitF h = WIDE4 ? trace_plain4(sc, o.x, o.y, o.z, d.x, d.y, d.z, smem_stack + threadIdx.x, blockDim.x)
+                           : trace_fast<false>(sc, o.x, o.y, o.z, d.x, d.y, d.z, __int_as_float(0x7f800000), 0xFFFFFFFFu);
             st_rec(&ps.hit[i], make_float4(__uint_as_float(h.prim), h.t, h.bx, h.by));
         }
     }

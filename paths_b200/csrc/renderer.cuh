@@ -84,7 +84,8 @@ struct TraceConfig {
     int sm_count = 148;
     int variant = 3;    // bounce and visibility rays: 0 plain batches (k_extend / k_shadow), 3 two-wide lane refill, 16 four-wide
     int variant_b0 = 1; // camera segment: 1 = k_camera_extend (raygen fused with a plain-batch closest hit), 0/3/16 = k_raygen + that kernel
-    int grid_trace = 0, grid_camera = 0, grid4 = 0;
+    int grid_trace = 0, grid_camera = 0, grid4 = 0, grid_camera4 = 0;
+    bool camera_wide4 = false; // camera segment over the four-wide nodes (scenes above 64k primitives)
     size_t smem4 = 0;
 };
 
@@ -103,12 +104,17 @@ template <typename R> paths_status configure_trace(const SceneDevice *sd, TraceC
     // (measured: teapot 7.5 vs 7.8 ms, dragon 25.4 vs 24.4 ms per 16 spp; profiles/r01_*)
     tc.variant = sd->view.n_prims > 65536u ? 16 : 3;
     tc.variant_b0 = 1;
+#ifndef PATHS_CAMERA_WIDE4_DEFAULT
+#define PATHS_CAMERA_WIDE4_DEFAULT 1
+#endif
+    tc.camera_wide4 = PATHS_CAMERA_WIDE4_DEFAULT && tc.variant == 16;
 #ifdef PATHS_DEV_SWITCHES /* development builds only (make EXTRA=-DPATHS_DEV_SWITCHES): a stale variable must not change a release run */
     if (const char *v = getenv("PATHS_EXTEND_VARIANT")) {
         int want = atoi(v);
         if (want == 0 || want == 3 || want == 16) tc.variant = want;
     }
     if (const char *v = getenv("PATHS_EXTEND_B0")) tc.variant_b0 = atoi(v);
+    if (const char *v = getenv("PATHS_CAMERA_WIDE4")) tc.camera_wide4 = atoi(v) != 0 && tc.variant == 16;
 #endif
     int bps = 0;
     if constexpr (IsF64<R>::value) {
@@ -119,18 +125,22 @@ template <typename R> paths_status configure_trace(const SceneDevice *sd, TraceC
     } else {
         PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (PATHS_K_EXTEND2), 128, 0));
         tc.grid_trace = tc.sm_count * std::max(bps, 1);
-        PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_camera_extend<float>, 128, 0));
+        PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (k_camera_extend<float, false>), 128, 0));
         tc.grid_camera = tc.sm_count * std::max(bps, 1);
         // four-wide kernels: stack of 3 * depth + 1 levels per thread in shared memory
         tc.smem4 = (size_t)(3 * sd->view.fast4_depth + 1) * 128 * sizeof(int32_t);
         if (tc.smem4 > 200 * 1024 || !sd->view.fast4_nodes) {
             if (tc.variant == 16) tc.variant = 3; // pathological tree: the two-wide kernels keep their stack in local memory
             tc.smem4 = 0;
+            tc.camera_wide4 = false;
         } else {
             PATHS_CU(cudaFuncSetAttribute(PATHS_K_SHADOW4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc.smem4));
             PATHS_CU(cudaFuncSetAttribute(PATHS_K_EXTEND4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc.smem4));
             PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, PATHS_K_EXTEND4, 128, tc.smem4));
             tc.grid4 = tc.sm_count * std::max(bps, 1);
+            PATHS_CU(cudaFuncSetAttribute((k_camera_extend<float, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc.smem4));
+            PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (k_camera_extend<float, true>), 128, tc.smem4));
+            tc.grid_camera4 = tc.sm_count * std::max(bps, 1);
         }
     }
     return PATHS_OK;
@@ -147,8 +157,9 @@ template <typename R4> __global__ void k_scatter_pixels(const R4 *in, const uint
 }
 
 // ------------------------------------------------------------------ batch queries
-template <typename R, bool MIXED>
+template <typename R, bool MIXED, bool WIDE4 = false>
 __global__ void k_trace_closest(DevScene sc, const double *o, const double *d, uint32_t n, uint32_t *prim, double *t, double *bary) {
+    extern __shared__ int32_t smem_stack[];
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     double ox = o[3 * i], oy = o[3 * i + 1], oz = o[3 * i + 2], dx = d[3 * i], dy = d[3 * i + 1], dz = d[3 * i + 2];
@@ -159,7 +170,8 @@ __global__ void k_trace_closest(DevScene sc, const double *o, const double *d, u
                         : trace_ref(sc, mk3(ox, oy, oz), mk3(dx, dy, dz));
         p = h.prim; tt = h.t; bx = h.bx; by = h.by;
     } else {
-        HitF h = trace_fast<false>(sc, (float)ox, (float)oy, (float)oz, (float)dx, (float)dy, (float)dz, __int_as_float(0x7f800000), 0xFFFFFFFFu);
+        HitF h = WIDE4 ? trace_plain4(sc, (float)ox, (float)oy, (float)oz, (float)dx, (float)dy, (float)dz, smem_stack + threadIdx.x, blockDim.x)
+                       : trace_fast<false>(sc, (float)ox, (float)oy, (float)oz, (float)dx, (float)dy, (float)dz, __int_as_float(0x7f800000), 0xFFFFFFFFu);
         p = h.prim; tt = h.t; bx = h.bx; by = h.by;
     }
     prim[i] = p;
@@ -294,7 +306,20 @@ paths_status trace_closest_impl(const SceneDevice *sd, const double *o, const do
             staged = true;
         }
     }
-    if (!staged) k_trace_closest<R, MIXED><<<blocks, 128>>>(sd->view, d_o, d_d, (uint32_t)n, d_p, d_t, d_b);
+    if (!staged) {
+        bool wide = false;
+        if constexpr (!IsF64<R>::value) { // PATHS_TRACE_CAMERA: the routine the fused camera kernel runs for this scene
+            TraceConfig tc;
+            paths_status st = configure_trace<R>(sd, tc, err);
+            if (st != PATHS_OK) return st;
+            if (tc.camera_wide4 && tc.grid_camera4 > 0) {
+                PATHS_CU(cudaFuncSetAttribute((k_trace_closest<R, false, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc.smem4));
+                k_trace_closest<R, false, true><<<blocks, 128, tc.smem4>>>(sd->view, d_o, d_d, (uint32_t)n, d_p, d_t, d_b);
+                wide = true;
+            }
+        }
+        if (!wide) k_trace_closest<R, MIXED><<<blocks, 128>>>(sd->view, d_o, d_d, (uint32_t)n, d_p, d_t, d_b);
+    }
     PATHS_CU(cudaGetLastError());
     PATHS_CU(cudaDeviceSynchronize());
     PATHS_CU(cudaMemcpy(prim, d_p, n * 4, cudaMemcpyDeviceToHost));

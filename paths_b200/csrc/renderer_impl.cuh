@@ -328,8 +328,12 @@ template <typename R> class RendererImpl : public RendererBase {
         for (uint32_t b = 0; b < nb; b++) {
             tic(1);
             if (b == 0 && fused_camera) {
-                if constexpr (!IsF64<R>::value)
-                    k_camera_extend<float><<<tc_.grid_camera, 128, 0, cs_>>>(sd_->view, cam_, k0, k1, shard, s_base, n_slots, ps_, pc_, pc_.work);
+                if constexpr (!IsF64<R>::value) {
+                    if (tc_.camera_wide4 && tc_.grid_camera4 > 0)
+                        k_camera_extend<float, true><<<tc_.grid_camera4, 128, tc_.smem4, cs_>>>(sd_->view, cam_, k0, k1, shard, s_base, n_slots, ps_, pc_, pc_.work);
+                    else
+                        k_camera_extend<float, false><<<tc_.grid_camera, 128, 0, cs_>>>(sd_->view, cam_, k0, k1, shard, s_base, n_slots, ps_, pc_, pc_.work);
+                }
             } else launch_extend(b);
             toc();
             stats_.n_extend_launches++;
