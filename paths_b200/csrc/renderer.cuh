@@ -104,8 +104,11 @@ template <typename R> paths_status configure_trace(const SceneDevice *sd, TraceC
     // (measured: teapot 7.5 vs 7.8 ms, dragon 25.4 vs 24.4 ms per 16 spp; profiles/r01_*)
     tc.variant = sd->view.n_prims > 65536u ? 16 : 3;
     tc.variant_b0 = 1;
+    // measured and NOT adopted (profiles/r02p_cam4_ab.txt): the camera segment over the four-wide nodes is slower than over the two-wide
+    // ones even on the large scenes (dragon -1.5 %, environment.yml -10 % whole frame): coherent primary rays keep a warp together on the
+    // narrow nodes, and the wide kernel pays its sorting network and shared-memory stack for nothing.  Kept behind a build switch.
 #ifndef PATHS_CAMERA_WIDE4_DEFAULT
-#define PATHS_CAMERA_WIDE4_DEFAULT 1
+#define PATHS_CAMERA_WIDE4_DEFAULT 0
 #endif
     tc.camera_wide4 = PATHS_CAMERA_WIDE4_DEFAULT && tc.variant == 16;
 #ifdef PATHS_DEV_SWITCHES /* development builds only (make EXTRA=-DPATHS_DEV_SWITCHES): a stale variable must not change a release run */
