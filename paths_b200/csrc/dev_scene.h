@@ -123,23 +123,48 @@ struct ShardInfo {
     // 32-pixel line, so the rays a warp generates, shades and re-emits start closer together and agree on more of the tree.  Results do
     // not depend on the numbering (every pixel's samples are a function of (seed, pixel, sample) only).
     uint32_t tiles_x, tiles_x_magic; // tiles_x_magic = floor(2^32 / tiles_x) + 1
+    // Inside a tile the 32 pixels are in Morton order (x0 y0 x1 y1 x2), so the first 4 / 8 / 16 of them are a 2x2 / 4x2 / 4x4 block.
+    // SAMPLE GROUPS: with sg_log2 = g > 0 a batch of 32 consecutive slots holds 2^g consecutive samples of 32 >> g consecutive local
+    // pixels (g = 2: a 4 x 2 pixel block x 4 samples) instead of one sample of 32 pixels: the rays of a warp are then closer still.
+    // Needs n_local % 32 == 0 and the pass's sample count % 2^g == 0 (else g = 0).  n_blocks = n_local >> (5 - g).
+    uint32_t sg_log2, n_blocks, n_blocks_magic; // n_blocks_magic = floor(2^32 / n_blocks)
 #if defined(__CUDACC__)
     __device__ __forceinline__ uint32_t pixel_of(uint32_t lp) const {
         if (pixels) return pixels[lp];
         if (tiles_x == 0) return lp;
         const uint32_t tile = lp >> 5, in = lp & 31u;
-        uint32_t ty = __umulhi(tile, tiles_x_magic); // tile / tiles_x: exact for tile < 2^32 / tiles_x with this magic (tiles are < 2^25)
+        uint32_t ty = __umulhi(tile, tiles_x_magic); // tile / tiles_x: exact for tile < 2^32 / tiles_x with this magic (checked on the host)
         uint32_t tx = tile - ty * tiles_x;
-        return ((ty << 2) + (in >> 3)) * (tiles_x << 3) + (tx << 3) + (in & 7u);
+        const uint32_t x = (in & 1u) | ((in >> 1) & 2u) | ((in >> 2) & 4u), y = ((in >> 1) & 1u) | ((in >> 2) & 2u);
+        return ((ty << 2) + y) * (tiles_x << 3) + (tx << 3) + x;
     }
-    // slot -> (local pixel, sample within the pass); the estimate __umulhi(slot, magic) is at most one too small
+    // slot -> (local pixel, sample within the pass); the estimate __umulhi(., magic) is at most one too small
     __device__ __forceinline__ void split(uint32_t slot, uint32_t &lp, uint32_t &k) const {
-        k = __umulhi(slot, n_local_magic);
-        lp = slot - k * n_local;
-        if (lp >= n_local) {
-            lp -= n_local;
-            k += 1;
+        if (sg_log2 == 0) {
+            k = __umulhi(slot, n_local_magic);
+            lp = slot - k * n_local;
+            if (lp >= n_local) {
+                lp -= n_local;
+                k += 1;
+            }
+            return;
         }
+        const uint32_t batch = slot >> 5, j = slot & 31u, pl = 5u - sg_log2;
+        uint32_t sg = __umulhi(batch, n_blocks_magic);
+        uint32_t pb = batch - sg * n_blocks;
+        if (pb >= n_blocks) {
+            pb -= n_blocks;
+            sg += 1;
+        }
+        lp = (pb << pl) + (j & ((1u << pl) - 1u));
+        k = (sg << sg_log2) + (j >> pl);
+    }
+    // the inverse: where sample k of local pixel lp lives
+    __device__ __forceinline__ size_t slot_of(uint32_t lp, uint32_t k) const {
+        if (sg_log2 == 0) return (size_t)k * n_local + lp;
+        const uint32_t pl = 5u - sg_log2;
+        const uint32_t batch = (k >> sg_log2) * n_blocks + (lp >> pl);
+        return ((size_t)batch << 5) + ((k & ((1u << sg_log2) - 1u)) << pl) + (lp & ((1u << pl) - 1u));
     }
 #endif
 };

@@ -1008,7 +1008,7 @@ __global__ void __launch_bounds__(256) k_accumulate(PathState<typename Vec4T<R>:
         uint32_t pixel = shard.pixel_of(lp);
         R4 s = sums[pixel];
         for (uint32_t k = 0; k < spp_pass; k++) {
-            R4 c = ld_rec(&ps.col[(size_t)k * shard.n_local + lp]);
+            R4 c = ld_rec(&ps.col[shard.slot_of(lp, k)]);
             s.x += c.x * c.w;
             s.y += c.y * c.w;
             s.z += c.z * c.w;

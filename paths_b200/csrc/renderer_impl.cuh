@@ -7,6 +7,9 @@
 #ifndef PATHS_SHARD_TILE
 #define PATHS_SHARD_TILE 32u /* edge of the square image tiles dealt to the ranks under PATHS_SHARD_TILES */
 #endif
+#ifndef PATHS_SAMPLE_GROUP_LOG2
+#define PATHS_SAMPLE_GROUP_LOG2 0u /* samples per batch of 32 slots = 2^this (ShardInfo::split) */
+#endif
 #ifndef PATHS_EXTEND2_KI
 #define PATHS_EXTEND2_KI 12
 #endif
@@ -48,6 +51,7 @@ template <typename R> class RendererImpl : public RendererBase {
     TraceConfig tc_; // which traversal kernels this scene runs on (shared with the per-ray seam, renderer.cuh)
     int grid_shade_ = 0, grid_stream_ = 0, shade_variant_ = 1;
     bool camera_tiles_ = true;
+    uint32_t sample_group_log2_ = PATHS_SAMPLE_GROUP_LOG2;
     // device buffers
     R4 *sums_ = nullptr;
     // frame combine (NCCL): the communicator of this rank, the combined estimator on the root, tile-shard staging
@@ -248,6 +252,7 @@ template <typename R> class RendererImpl : public RendererBase {
 #ifdef PATHS_DEV_SWITCHES
         if (const char *v = getenv("PATHS_SHADE_VARIANT")) shade_variant_ = atoi(v);
         if (const char *v = getenv("PATHS_CAMERA_TILES")) camera_tiles_ = atoi(v) != 0;
+        if (const char *v = getenv("PATHS_SAMPLE_GROUP_LOG2")) sample_group_log2_ = (uint32_t)std::min(5, std::max(0, atoi(v)));
 #endif
         int bps = 0;
         {
@@ -315,6 +320,15 @@ template <typename R> class RendererImpl : public RendererBase {
             (uint64_t)(npix_ / 32) * (W_ / 8) < (1ull << 32)) { // the multiply-high division by tiles_x is exact below that
             shard.tiles_x = W_ / 8;
             shard.tiles_x_magic = (uint32_t)((1ull << 32) / shard.tiles_x) + 1u;
+        }
+        // sample groups: 2^g samples of 32 >> g neighbouring pixels per batch of 32 slots (ShardInfo)
+        shard.sg_log2 = 0;
+        shard.n_blocks = 0;
+        shard.n_blocks_magic = 0;
+        if (sample_group_log2_ > 0 && n_local % 32 == 0 && n_spp % (1u << sample_group_log2_) == 0) {
+            shard.sg_log2 = sample_group_log2_;
+            shard.n_blocks = n_local >> (5u - shard.sg_log2);
+            shard.n_blocks_magic = shard.n_blocks > 1 ? (uint32_t)((1ull << 32) / shard.n_blocks) : 0xFFFFFFFFu;
         }
         const uint32_t nb = opts_.max_bounces + 1; // segments per path (trace.rs:13-16)
         PATHS_CU(cudaMemsetAsync(ctl_block_, 0, n_ctl_ * sizeof(uint32_t), cs_));
@@ -512,11 +526,11 @@ template <typename R> class RendererImpl : public RendererBase {
                 if ((ty * tiles_x + tx) % world != rank) continue;
                 for (uint32_t by = 0; by < T; by += 4)
                     for (uint32_t bx = 0; bx < T; bx += 8)
-                        for (uint32_t iy = 0; iy < 4; iy++)
-                            for (uint32_t ix = 0; ix < 8; ix++) {
-                                const uint32_t x = tx * T + bx + ix, y = ty * T + by + iy;
-                                if (x < W && y < H) own.push_back(x + y * W);
-                            }
+                        for (uint32_t in = 0; in < 32; in++) { // Morton order inside the block, like ShardInfo::pixel_of
+                            const uint32_t ix = (in & 1u) | ((in >> 1) & 2u) | ((in >> 2) & 4u), iy = ((in >> 1) & 1u) | ((in >> 2) & 2u);
+                            const uint32_t x = tx * T + bx + ix, y = ty * T + by + iy;
+                            if (x < W && y < H) own.push_back(x + y * W);
+                        }
             }
     }
     // Renderer::drain_result_queue -> Estimator::update_pixel (renderer.rs:93-105) across GPUs: partial estimators of all ranks are
