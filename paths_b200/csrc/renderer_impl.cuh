@@ -8,7 +8,9 @@
 #define PATHS_SHARD_TILE 32u /* edge of the square image tiles dealt to the ranks under PATHS_SHARD_TILES */
 #endif
 #ifndef PATHS_SAMPLE_GROUP_LOG2
-#define PATHS_SAMPLE_GROUP_LOG2 0u /* samples per batch of 32 slots = 2^this (ShardInfo::split) */
+/* samples per batch of 32 slots = 2^this (ShardInfo::split).  Same box, whole frame, M samples/s (profiles/r02q_sg_ab.txt): teapot 3945 / 3987 / 4042 /
+ * 4047, environment.yml 7477 / 7677 / 7575 / 7742, dragon 1132 / 1137 / 1143 / 1150, bunny 2884 / 2882 / 2907 / 2946 for 1 / 2 / 4 / 8 samples */
+#define PATHS_SAMPLE_GROUP_LOG2 3u
 #endif
 #ifndef PATHS_EXTEND2_KI
 #define PATHS_EXTEND2_KI 12
@@ -325,8 +327,10 @@ template <typename R> class RendererImpl : public RendererBase {
         shard.sg_log2 = 0;
         shard.n_blocks = 0;
         shard.n_blocks_magic = 0;
-        if (sample_group_log2_ > 0 && n_local % 32 == 0 && n_spp % (1u << sample_group_log2_) == 0) {
-            shard.sg_log2 = sample_group_log2_;
+        uint32_t g = sample_group_log2_;
+        while (g > 0 && n_spp % (1u << g) != 0) g--; // the largest group size that divides this pass's sample count
+        if (g > 0 && n_local % 32 == 0) {
+            shard.sg_log2 = g;
             shard.n_blocks = n_local >> (5u - shard.sg_log2);
             shard.n_blocks_magic = shard.n_blocks > 1 ? (uint32_t)((1ull << 32) / shard.n_blocks) : 0xFFFFFFFFu;
         }
