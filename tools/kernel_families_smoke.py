@@ -1,5 +1,6 @@
-"""Small workload for compute-sanitizer (memcheck / racecheck / initcheck): every kernel family once, tiny sizes.
-    compute-sanitizer --tool memcheck python tools/sanitize_smoke.py"""
+"""Every kernel family once at tiny sizes (f32 / f64 / mixed, host and device tree builders, preview, column sweeps, whole frames).
+Written as the workload for compute-sanitizer, which is closed on this pool; it now runs under the debug-assert build instead
+(tools/run_asserts.sh sets PATHS_B200_LIB to the build made with -DPATHS_DEBUG_ASSERTS and checks its counters afterwards)."""
 import sys
 from pathlib import Path
 
