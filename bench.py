@@ -403,7 +403,20 @@ def run_ours(args, rank, world, local_rank):
             multi_gpu_check["how"] = ("N-rank frame combined by paths_renderer_combine (NCCL inside libpaths_b200.so) vs the same frame rendered "
                                       "by one renderer on rank 0; tiles must be bit-identical, sample shards within rtol 2e-6")
 
-    # ---- BASELINE's other configs (dragon; environment tile-sharded): short device-timed legs of the same step
+    # ---- strong scaling of the headline scene: a fixed frame of `spp_frame` samples per pixel split over the N ranks (256 spp),
+    # combine inside the timed region; at N = 1 the same frame on one GPU, so that the driver's 1 / 2 / 4 / 8 runs give the curve
+    strong = None
+    if args.scaling == "weak" and not args.no_strong:
+        rs = make_renderer(scene, False, args.shard)
+        ks = 3
+        ms_s, ranks_s, d_s, _, _ = timed_region(rs, ks, 3, args.spp_frame, False)
+        rs.shutdown()
+        smp_s, = totals(d_s, ("samples",))
+        strong = {"scaling": "strong", "spp_frame": args.spp_frame, "value": smp_s / (ms_s * 1e-3), "unit": UNIT, "ms_per_frame": ms_s / ks, "steps": ks,
+                  "warmup": 3, "n_gpus": world, "rank_ms_max": max(ranks_s) / ks, "rank_ms_mean": sum(ranks_s) / len(ranks_s) / ks,
+                  "what": f"{yaml} at {W}x{H}: one {args.spp_frame}-spp frame per step in total, {args.shard} shards, combine on rank 0 inside the timed region"}
+
+    # ---- BASELINE's other configs (dragon; environment and doom tile-sharded): short device-timed legs of the same step
     others = {}
     for label, name, shard in legs:
         ensure_assets(name)
@@ -516,6 +529,8 @@ def run_ours(args, rank, world, local_rank):
         }
         if multi_gpu_check is not None:
             line["multi_gpu_check"] = multi_gpu_check
+        if strong is not None:
+            line["strong_scaling"] = strong
         if others:
             line["other_scenes"] = others
     if world > 1:
@@ -539,7 +554,8 @@ def main():
                     help="N > 1: each GPU renders a sample range of every pixel (default) or all samples of its 32x32 tiles")
     ap.add_argument("--precision", type=int, default=0, choices=[0, 32, 48, 64])
     ap.add_argument("--seed", type=int, default=1)
-    ap.add_argument("--also", default="dragon,environment:tiles",
+    ap.add_argument("--no-strong", action="store_true", help="skip the short strong-scaling leg of the default run")
+    ap.add_argument("--also", default="dragon,environment:tiles,doom:tiles",
                     help="comma-separated extra legs `scene[:shard]` timed briefly after the teapot headline (none = skip)")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for the cpu_baseline leg")
     ap.add_argument("--no-check", action="store_true", help="skip the N-GPU = 1-GPU frame check (N > 1)")
