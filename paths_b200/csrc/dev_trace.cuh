@@ -207,6 +207,9 @@ struct HitF {
 };
 
 #define PATHS_FAST_STACK 64
+#ifndef PATHS_INNER_SELECT
+#define PATHS_INNER_SELECT 0 /* two-wide inner node: child choice with selects and a predicated push instead of a four-way branch */
+#endif
 // A two-wide traversal holds at most one postponed sibling per tree level, and both builders refuse trees deeper than 60 levels
 // (bvh_fast.cpp: error; bvh_device.cu: falls back to the host builder), so the 64-entry stack cannot overflow.  The release kernels keep a
 // predicated store (an atomic in this cold branch cost 8-12 % of the closest-hit kernels' time: measured, profiles/r02c_ab.txt); the
@@ -264,6 +267,16 @@ template <bool ANY> __device__ __forceinline__ HitF trace_fast(const DevScene &s
             float tf1 = fminf(fminf(fmaxf(b0, b1), fmaxf(b2, b3)), fminf(fmaxf(b4, b5), best.t)) * 1.0000004f;
             bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
             int32_t c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
+#if PATHS_INNER_SELECT
+            const bool both = h0 && h1, any = h0 || h1, first0 = tn0 <= tn1;
+            const int32_t near = (h0 && (!h1 || first0)) ? c0 : c1, far = first0 ? c1 : c0;
+            if (both) stack_push(stack, sp, far);
+            node = near;
+            if (!any) {
+                if (sp == 0) return best;
+                node = stack[--sp];
+            }
+#else
             if (h0 && h1) {
                 bool first0 = tn0 <= tn1;
                 node = first0 ? c0 : c1;
@@ -274,6 +287,7 @@ template <bool ANY> __device__ __forceinline__ HitF trace_fast(const DevScene &s
                 if (sp == 0) return best;
                 node = stack[--sp];
             }
+#endif
         }
         // leaf: up to 8 slots of 3 x float4
         {
@@ -435,6 +449,19 @@ struct TravF {
         float tf1 = fminf(fminf(fmaxf(b0, b1), fmaxf(b2, b3)), fminf(fmaxf(b4, b5), t)) * 1.0000004f;
         bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
         int32_t c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
+#if PATHS_INNER_SELECT
+        // one predicated store and one predicated load instead of a four-way branch: the four outcomes (both / left / right / none)
+        // ran one after the other at 4-5 active lanes each (ncu source page: push and pop 7.3 % of the kernel's warp instructions)
+        const bool both = h0 && h1, any = h0 || h1, first0 = tn0 <= tn1;
+        const int32_t near = (h0 && (!h1 || first0)) ? c0 : c1, far = first0 ? c1 : c0;
+        if (both) stack_push(stack, sp, far);
+        int32_t next = near;
+        if (!any) {
+            next = PATHS_TRAV_DONE;
+            if (sp > 0) next = stack[--sp];
+        }
+        node = next;
+#else
         if (h0 && h1) {
             bool first0 = tn0 <= tn1;
             node = first0 ? c0 : c1;
@@ -442,6 +469,7 @@ struct TravF {
         } else if (h0) node = c0;
         else if (h1) node = c1;
         else node = sp > 0 ? stack[--sp] : PATHS_TRAV_DONE;
+#endif
     }
     // one leaf (node < 0, not DONE): tests its primitives, then pops.  Returns true when ANY and something was hit.
     template <bool ANY> __device__ __forceinline__ bool leaf(const float4 *__restrict__ leaves, int32_t *stack, uint32_t skip_prim) {
