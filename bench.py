@@ -55,8 +55,9 @@ def ensure_assets(scene):
 
 
 def also_legs(args, world):
-    """BASELINE.json quotes the metric on teapot AND dragon, and names environment tile-sharded as config 5: the default (teapot) run
-    of our arm adds short legs for them, outside the headline's timed region.  -> [(label, scene, shard)]"""
+    """BASELINE.json quotes the metric on teapot AND dragon, and names environment + doom tile-sharded as config 5; teapot_light is the
+    headline mesh with next-event estimation: the default (teapot) run of our arm adds short legs for them, outside the
+    headline's timed region.  -> [(label, scene, shard)]"""
     if args.impl != "ours" or args.scene != "teapot" or args.also in ("", "none"):
         return []
     legs = []
@@ -555,7 +556,7 @@ def main():
     ap.add_argument("--precision", type=int, default=0, choices=[0, 32, 48, 64])
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--no-strong", action="store_true", help="skip the short strong-scaling leg of the default run")
-    ap.add_argument("--also", default="dragon,environment:tiles,doom:tiles",
+    ap.add_argument("--also", default="dragon,teapot_light,environment:tiles,doom:tiles",
                     help="comma-separated extra legs `scene[:shard]` timed briefly after the teapot headline (none = skip)")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for the cpu_baseline leg")
     ap.add_argument("--no-check", action="store_true", help="skip the N-GPU = 1-GPU frame check (N > 1)")
