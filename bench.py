@@ -82,7 +82,7 @@ def make_config(args, world, prims):
     return {"workload": f"{yaml} at {W}x{H}, {what}" + SYNTHETIC.get(args.scene, ""), "scene": args.scene, "width": W, "height": H,
             "spp_per_step_per_gpu": args.spp_step if args.scaling == "weak" else args.spp_frame / max(world, 1), "prims": prims, "seed": args.seed,
             "shard": args.shard, "scaling": args.scaling,
-            "l2": "per-pass path state (33M slots x 136 B = 4.5 GB per pass context) streams through HBM and exceeds the 126 MB L2; the scene tables "
+            "l2": "per-pass path state (33M slots x 176 B = 5.8 GB per pass context) streams through HBM and exceeds the 126 MB L2; the scene tables "
                   "(BVH + triangles, ~1 MB for teapot) are L2-resident by design"}
 
 
