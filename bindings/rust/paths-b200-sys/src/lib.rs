@@ -15,6 +15,7 @@ pub const PATHS_PRECISION_AUTO: i32 = 0;
 pub const PATHS_PRECISION_F32: i32 = 32;
 pub const PATHS_PRECISION_MIXED: i32 = 48;
 pub const PATHS_PRECISION_F64: i32 = 64;
+pub const PATHS_STATIC_MAX_RAYS: usize = 65536;
 pub const PATHS_TRACE_CAMERA: i32 = 33;
 pub const PATHS_TRACE_TWO_WIDE: i32 = 34;
 pub const PATHS_TRACE_PLAIN: i32 = 35;
@@ -113,6 +114,9 @@ extern "C" {
     // per-ray seams (BVH::find_intersection, src/bvh.rs:78-140; the shadow query of trace_ray, src/trace.rs:61-66)
     pub fn paths_trace_closest(s: *mut paths_scene, device: i32, origins: *const f64, dirs: *const f64, n: usize,
                                prim_id: *mut u32, t: *mut f64, bary: *mut f64, precision: i32) -> i32;
+    // no reference counterpart: paths_trace_closest (f32) with its scratch in a static device array, at most PATHS_STATIC_MAX_RAYS rays
+    pub fn paths_trace_closest_static(s: *mut paths_scene, device: i32, origins: *const f64, dirs: *const f64, n: usize,
+                                      prim_id: *mut u32, t: *mut f64, bary: *mut f64) -> i32;
     pub fn paths_trace_occluded(s: *mut paths_scene, device: i32, origins: *const f64, dirs: *const f64, light: *const u32, n: usize,
                                 occluded: *mut u8, precision: i32) -> i32;
     // renderer (Renderer, src/renderer.rs:33-141)

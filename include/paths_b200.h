@@ -245,6 +245,24 @@ paths_status paths_trace_closest(paths_scene *s, int32_t device, const double *o
 paths_status paths_trace_occluded(paths_scene *s, int32_t device, const double *origins, const double *dirs, const uint32_t *light,
                                   size_t n, uint8_t *occluded, int32_t precision);
 
+/* paths_trace_closest (precision 32) for callers that may not allocate device memory.  NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc.  Same
+ * rays in, same answers out (the production closest-hit kernel a render of this scene launches for its bounce rays; bary may be NULL),
+ * but every byte of device scratch comes from one file-scope `static __device__` array inside the library -- PATHS_STATIC_SCRATCH_BYTES
+ * (8.25 MiB) that every GPU which loads the library holds until exit -- and the call makes no cudaMalloc / cudaFree or any allocating
+ * library call.  Limits and rules:
+ *   - n <= PATHS_STATIC_MAX_RAYS (65536) per call, else PATHS_ERR_INVALID_ARG with the limit in paths_last_error(); split larger batches;
+ *   - the scene must ALREADY be staged on `device` with its production tree (staging allocates): any earlier paths_trace_closest /
+ *     paths_trace_occluded with precision 32 or 48, paths_scene_check_bvh or paths_renderer_create on that device does it; otherwise
+ *     PATHS_ERR_UNSUPPORTED;
+ *   - all calls share the one array, which keeps the last call's contents; each call rewrites what it reads.  Calls that overlap on one
+ *     GPU would race on it: the library serialises the calls of a process with a lock and each call waits for the device before it
+ *     returns (every process has its own copy of the array). */
+#define PATHS_STATIC_MAX_RAYS 65536u
+#define PATHS_STATIC_SCRATCH_BYTES (256u + PATHS_STATIC_MAX_RAYS * 132u) /* counters + 132 B per ray: staged rays, records, answers */
+paths_status paths_trace_closest_static(paths_scene *s, int32_t device, const double *origins, const double *dirs, size_t n,
+                                        uint32_t *prim_id, double *t, double *bary);
+
 /* ------------------------------------------------------------------ renderer (replaces Renderer, src/renderer.rs:33-141) */
 
 void paths_render_opts_default(paths_render_opts *o);

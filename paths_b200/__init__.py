@@ -201,6 +201,20 @@ class Scene:
         check(lib().paths_trace_closest(self._h, device, _p(o), _p(d), n, _p(prim), _p(t), _p(bary) if want_bary else None, precision))
         return (prim, t, bary) if want_bary else (prim, t)
 
+    STATIC_MAX_RAYS = 65536  # PATHS_STATIC_MAX_RAYS
+
+    def find_intersection_static(self, origins, dirs, device=0, want_bary=False):
+        """paths_trace_closest_static: find_intersection(precision=32) with every byte of device scratch in a static device array of the
+        library (no allocation; at most STATIC_MAX_RAYS rays; the scene must already be staged on the device).  No reference counterpart."""
+        o = np.ascontiguousarray(origins, dtype=np.float64).reshape(-1, 3)
+        d = np.ascontiguousarray(dirs, dtype=np.float64).reshape(-1, 3)
+        n = o.shape[0]
+        prim = np.empty(n, dtype=np.uint32)
+        t = np.empty(n, dtype=np.float64)
+        bary = np.empty((n, 3), dtype=np.float64) if want_bary else None
+        check(lib().paths_trace_closest_static(self._h, device, _p(o), _p(d), n, _p(prim), _p(t), _p(bary) if want_bary else None))
+        return (prim, t, bary) if want_bary else (prim, t)
+
     def occluded(self, origins, dirs, light=None, precision=PRECISION_F32, device=0):
         """The shadow query of trace_ray (src/trace.rs:61-66) over a batch of rays, through the visibility kernel a render launches.
         light: index (or per-ray indices) of the light the rays were sampled toward, None = every hit occludes.  -> uint8 flags."""

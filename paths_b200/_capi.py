@@ -124,6 +124,7 @@ SIGNATURES = {
     "paths_scene_prim_geometry": (C.c_int, [VP, C.c_uint32, VP, C.POINTER(C.c_int32)]),
     "paths_scene_prim_entity": (C.c_int, [VP, C.c_uint32, C.POINTER(C.c_int32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
     "paths_trace_closest": (C.c_int, [VP, C.c_int32, VP, VP, C.c_size_t, VP, VP, VP, C.c_int32]),
+    "paths_trace_closest_static": (C.c_int, [VP, C.c_int32, VP, VP, C.c_size_t, VP, VP, VP]),
     "paths_trace_occluded": (C.c_int, [VP, C.c_int32, VP, VP, VP, C.c_size_t, VP, C.c_int32]),
     "paths_render_opts_default": (None, [C.POINTER(RenderOpts)]),
     "paths_renderer_create": (C.c_int, [VP, C.POINTER(Camera), C.POINTER(RenderOpts), C.POINTER(VP)]),

@@ -585,6 +585,29 @@ paths_status paths_trace_closest(paths_scene *s, int32_t device, const double *o
     PATHS_GUARD_END
 }
 
+// No counterpart in the reference: the f32 per-ray seam with its scratch in a static
+// device array.  Nothing on this path allocates: a scene that is not staged on the device yet is refused instead of staged.
+paths_status paths_trace_closest_static(paths_scene *s, int32_t device, const double *origins, const double *dirs, size_t n, uint32_t *prim_id,
+                                        double *t, double *bary) {
+    PATHS_GUARD_BEGIN
+    if (!s || (n && (!origins || !dirs || !prim_id || !t))) return fail(PATHS_ERR_INVALID_ARG, "null argument");
+    paths_status st = check_device(device);
+    if (st != PATHS_OK) return st;
+    const SceneDevice *sd = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(s->mu);
+        for (paths_scene::Staged &e : s->staged)
+            if (!sd && e.sd->device == device && e.fast) sd = e.sd; // the copy ensure_staged would hand paths_trace_closest
+    }
+    if (!sd)
+        return fail(PATHS_ERR_UNSUPPORTED, "paths_trace_closest_static: the scene is not staged on this device yet (staging allocates; call "
+                                           "paths_trace_closest, paths_scene_check_bvh or paths_renderer_create on it once first)");
+    std::string err;
+    st = trace_closest_static_f32(sd, origins, dirs, n, prim_id, t, bary, err);
+    return st == PATHS_OK ? st : fail(st, err);
+    PATHS_GUARD_END
+}
+
 paths_status paths_trace_occluded(paths_scene *s, int32_t device, const double *origins, const double *dirs, const uint32_t *light, size_t n,
                                   uint8_t *occluded, int32_t precision) {
     PATHS_GUARD_BEGIN

@@ -70,6 +70,9 @@ RendererBase *make_renderer_f64(const SceneDevice *sd, const paths_camera &cam, 
 // kernel: 0 = the bounce-ray kernel a render launches for this scene, or a PATHS_TRACE_* code
 paths_status trace_closest_f32(const SceneDevice *sd, const double *o, const double *d, size_t n, uint32_t *prim, double *t, double *bary,
                                int kernel, std::string &err);
+// paths_trace_closest_static: the same kernels with all scratch in a file-scope device array of kernels_f32.cu (no allocation)
+paths_status trace_closest_static_f32(const SceneDevice *sd, const double *o, const double *d, size_t n, uint32_t *prim, double *t, double *bary,
+                                      std::string &err);
 paths_status trace_occluded_f32(const SceneDevice *sd, const double *o, const double *d, const uint32_t *light, size_t n, uint8_t *occluded,
                                 int kernel, std::string &err);
 paths_status trace_occluded_f64(const SceneDevice *sd, const double *o, const double *d, const uint32_t *light, size_t n, uint8_t *occluded,
