@@ -11,7 +11,7 @@ print("library:", pb.lib().paths_version().decode(), "from", pb._capi.LIB_PATH)
 assert b"+asserts" in pb.lib().paths_version()
 PY
 python tools/kernel_families_smoke.py 2>&1 | tail -3
-python -m pytest tests/test_gpu_production_rays.py tests/test_gpu_parity.py tests/test_gpu_extensions.py tests/test_gpu_frontend.py tests/test_gpu_edges.py -q -m gpu -p no:cacheprovider 2>&1 | tail -6
+python -m pytest tests/test_gpu_production_rays.py tests/test_gpu_parity.py tests/test_gpu_extensions.py tests/test_gpu_frontend.py tests/test_gpu_edges.py tests/test_zz_no_alloc.py -q -m gpu -p no:cacheprovider 2>&1 | tail -6
 python - <<'PY'
 import paths_b200 as pb
 for name, prec in (("teapot", 32), ("bunny", 32), ("dragon", 32), ("bunny", 48)):
