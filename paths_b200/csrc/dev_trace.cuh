@@ -515,6 +515,74 @@ struct TravF {
     }
 };
 
+// Mixed mode, resumable: trace_mixed cut into the same bounded steps as TravF (f32 slab tests over the production two-wide tree, the
+// reference's f64 primitive tests at the leaves, the same visiting order and acceptance rule), so that k_extend_refill_m /
+// k_shadow_refill_m can refill lanes.  A ray's answer is bit-identical to trace_mixed's: only the interleaving of lanes changes.
+struct TravM {
+    D3v o, d;
+    float idx, idy, idz, oix, oiy, oiz, tbound;
+    double t, bx, by;
+    uint32_t prim;
+    int32_t node;
+    int sp;
+
+    template <bool ANY> __device__ __forceinline__ void init(D3v o_, D3v d_, double tmax, int32_t root) {
+        o = o_; d = d_;
+        const float ox = (float)o.x, oy = (float)o.y, oz = (float)o.z, dx = (float)d.x, dy = (float)d.y, dz = (float)d.z;
+        const float eps = 8.27180613e-25f;
+        idx = 1.0f / (fabsf(dx) > eps ? dx : copysignf(eps, dx));
+        idy = 1.0f / (fabsf(dy) > eps ? dy : copysignf(eps, dy));
+        idz = 1.0f / (fabsf(dz) > eps ? dz : copysignf(eps, dz));
+        oix = -ox * idx; oiy = -oy * idy; oiz = -oz * idz;
+        tbound = ANY ? __double2float_ru(tmax) : __int_as_float(0x7f800000);
+        t = tmax; bx = by = 0.0;
+        prim = 0xFFFFFFFFu;
+        node = root; // an empty tree's root is PATHS_TRAV_DONE itself
+        sp = 0;
+    }
+    __device__ __forceinline__ void inner(const float4 *__restrict__ nodes, int32_t *stack) {
+        const float4 n0 = __ldg(nodes + 4 * node), n1 = __ldg(nodes + 4 * node + 1), n2 = __ldg(nodes + 4 * node + 2), n3 = __ldg(nodes + 4 * node + 3);
+        // explicit fma: the f64 translation unit is compiled with -fmad=false
+        float a0 = __fmaf_rn(n0.x, idx, oix), a1 = __fmaf_rn(n0.y, idx, oix), a2 = __fmaf_rn(n0.z, idy, oiy), a3 = __fmaf_rn(n0.w, idy, oiy);
+        float a4 = __fmaf_rn(n2.x, idz, oiz), a5 = __fmaf_rn(n2.y, idz, oiz);
+        float tn0 = fmaxf(fmaxf(fminf(a0, a1), fminf(a2, a3)), fmaxf(fminf(a4, a5), 0.0f));
+        float tf0 = fminf(fminf(fmaxf(a0, a1), fmaxf(a2, a3)), fminf(fmaxf(a4, a5), tbound)) * 1.0000004f;
+        float b0 = __fmaf_rn(n1.x, idx, oix), b1 = __fmaf_rn(n1.y, idx, oix), b2 = __fmaf_rn(n1.z, idy, oiy), b3 = __fmaf_rn(n1.w, idy, oiy);
+        float b4 = __fmaf_rn(n2.z, idz, oiz), b5 = __fmaf_rn(n2.w, idz, oiz);
+        float tn1 = fmaxf(fmaxf(fminf(b0, b1), fminf(b2, b3)), fmaxf(fminf(b4, b5), 0.0f));
+        float tf1 = fminf(fminf(fmaxf(b0, b1), fmaxf(b2, b3)), fminf(fmaxf(b4, b5), tbound)) * 1.0000004f;
+        bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
+        int32_t c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
+        if (h0 && h1) {
+            bool first0 = tn0 <= tn1;
+            node = first0 ? c0 : c1;
+            stack_push(stack, sp, first0 ? c1 : c0);
+        } else if (h0) node = c0;
+        else if (h1) node = c1;
+        else node = sp > 0 ? stack[--sp] : PATHS_TRAV_DONE;
+    }
+    // one leaf, then pop.  Returns true when ANY and a primitive other than skip_prim was hit closer than the bound.
+    template <bool ANY> __device__ __forceinline__ bool leaf(const DevScene &sc, const float4 *__restrict__ leaves, int32_t *stack, uint32_t skip_prim) {
+        uint32_t code = (uint32_t)~node;
+        uint32_t first = code >> 3, cnt = (code & 7u) + 1u;
+        for (uint32_t k = 0; k < cnt; k++) {
+            uint32_t p = __float_as_uint(__ldg(leaves + 3 * (first + k) + 2).w) & 0x7FFFFFFFu;
+            if (ANY && p == skip_prim) continue;
+            double tt, hx, hy;
+            if (prim_hit64(sc, p, o, d, tt, hx, hy)) {
+                // src/bvh.rs:93-104: the first hit is taken as it is (even t = inf), later ones only when strictly closer
+                if (ANY ? tt < t : (prim == 0xFFFFFFFFu || tt < t)) {
+                    prim = p; t = tt; bx = hx; by = hy;
+                    if (ANY) return true;
+                    tbound = __double2float_ru(tt);
+                }
+            }
+        }
+        node = sp > 0 ? stack[--sp] : PATHS_TRAV_DONE;
+        return false;
+    }
+};
+
 // ------------------------------------------------------------------ four-wide traversal, stack in shared memory
 // Node = one 128-byte line: six float4 rows {lo.x, hi.x, lo.y, hi.y, lo.z, hi.z} over the four children + their codes.
 // Hit children are sorted by entry distance with a 5-exchange network; the nearest is entered, the rest are pushed far-first.

@@ -536,10 +536,21 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LI
                 if (!first) prefetch_l2(tin + in);
             }
         }
-        if (base >= count) break;
         uint32_t i = base + lane;
         const bool in_range = i < count;
         if constexpr (PARK) {
+        // f64: ONE call site for shade_batch -- the last, partial group of parked hits goes through the loop too.  (With a second call
+        // after the loop the f64 instantiation was not inlined: its closure and the kernel's parameter block went to a 928-byte local
+        // frame per thread, which does not fit L1 beside the staging buffers -- profiles/r02zz_doom_shade_*.)  The f32 instantiations
+        // inline both calls and keep the tail after the loop (one register less in the loop).
+        bool valid = true;
+        if (base >= count) {
+            if (!IsF64<R>::value || npark == 0) break;
+            __syncwarp();
+            valid = lane < npark;
+            i = valid ? park[lane] : 0u;
+            npark = 0; // the next fetch is past the end again, and nothing is parked: the loop ends
+        } else {
         // Rays that left the scene are finished at once; hits are PARKED (their queue positions, per warp, in shared memory) and shaded 32
         // at a time, so that the long material / sampling code runs with full warps (ncu on teapot bounce 1, where 45 % of the rays
         // miss: 15 of 32 lanes per instruction before).  Records are dense and prefetched, so the parked gather costs no extra latency.
@@ -571,12 +582,18 @@ __global__ void __launch_bounds__(128, (IsF64<R>::value ? PATHS_LB_SHADE64 : (LI
         __syncwarp();
         if (lane < left) park[lane] = moved;
         npark = left;
-        shade_batch(true, i);
-        } else shade_batch(in_range, i);
+        }
+        shade_batch(valid, i);
+        } else {
+            if (base >= count) break;
+            shade_batch(in_range, i);
+        }
     }
-    if (PARK && npark > 0) { // the last, partial group of parked hits
-        __syncwarp();
-        shade_batch(lane < npark, lane < npark ? park[lane] : 0u);
+    if constexpr (PARK && !IsF64<R>::value) {
+        if (npark > 0) { // the last, partial group of parked hits
+            __syncwarp();
+            shade_batch(lane < npark, lane < npark ? park[lane] : 0u);
+        }
     }
     if (LIGHTS && sfill > 0) {
         __syncwarp();
@@ -780,6 +797,122 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_shadow_refill(DevScene
                     st_rec(&ps.col[slot], col);
                     has = false;
                 }
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ mixed mode with lane refill (f64 records, TravM)
+// The plain batches of k_extend<double, true> leave a warp waiting for its slowest ray (doom.yml at 1080p: 95 of 189 ms per 32 spp in
+// extend).  Same schedule as k_extend_refill over the f64 path state; every ray's answer is bit-identical to trace_mixed's.
+#ifndef PATHS_M2_MIN
+#define PATHS_M2_MIN 16
+#endif
+#ifndef PATHS_M2_KI
+#define PATHS_M2_KI 8
+#endif
+#define PATHS_K_EXTEND2M k_extend_refill_m<PATHS_M2_MIN, PATHS_M2_KI>
+#define PATHS_K_SHADOW2M k_shadow_refill_m<PATHS_M2_MIN, PATHS_M2_KI>
+template <int MIN_REFILL, int KI>
+__global__ void __launch_bounds__(128) k_extend_refill_m(DevScene sc, const double4 *__restrict__ rays, double4 *__restrict__ hits,
+                                                         const uint32_t *count_ptr, uint32_t *cursor) {
+    const uint32_t count = *count_ptr;
+    const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    const float4 *__restrict__ nodes = sc.fast_nodes;
+    const float4 *__restrict__ leaves = sc.fast_leaves;
+    int32_t stack[PATHS_FAST_STACK];
+    TravM tv;
+    tv.node = PATHS_TRAV_DONE;
+    bool has = false, exhausted = false;
+    uint32_t slot = 0;
+    for (;;) {
+        unsigned idle = __ballot_sync(PATHS_FULL_MASK, !has);
+        int n = __popc(idle);
+        if (!exhausted && n >= MIN_REFILL) {
+            int leader = __ffs(idle) - 1;
+            uint32_t base = 0;
+            if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)n);
+            base = __shfl_sync(PATHS_FULL_MASK, base, leader);
+            if (!has) {
+                uint32_t i = base + __popc(idle & lt);
+                if (i < count) {
+                    slot = i;
+                    double4 o = ld_rec(&rays[2 * (size_t)i]), d = ld_rec(&rays[2 * (size_t)i + 1]);
+                    tv.init<false>(mk3(o.x, o.y, o.z), mk3(d.x, d.y, d.z), (double)__int_as_float(0x7f800000), sc.fast_root);
+                    has = true;
+                }
+            }
+            exhausted = base + (uint32_t)n >= count;
+        }
+        if (!__any_sync(PATHS_FULL_MASK, has)) break;
+        if (has) {
+#pragma unroll 1
+            for (int k = 0; k < KI && tv.node >= 0; k++) tv.inner(nodes, stack);
+            if (tv.node < 0 && tv.node != PATHS_TRAV_DONE) tv.leaf<false>(sc, leaves, stack, 0xFFFFFFFFu);
+            if (tv.node == PATHS_TRAV_DONE) {
+                st_rec(&hits[slot], mk4(bits_to_real(tv.prim, 0.0), tv.t, tv.bx, tv.by));
+                has = false;
+            }
+        }
+    }
+}
+
+template <int MIN_REFILL, int KI>
+__global__ void __launch_bounds__(128) k_shadow_refill_m(DevScene sc, PathState<double4> ps, const uint32_t *count_ptr, uint32_t *cursor,
+                                                         unsigned long long *totals) {
+    const uint32_t count = *count_ptr;
+    const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    const float4 *__restrict__ nodes = sc.fast_nodes;
+    const float4 *__restrict__ leaves = sc.fast_leaves;
+    int32_t stack[PATHS_FAST_STACK];
+    TravM tv;
+    tv.node = PATHS_TRAV_DONE;
+    bool has = false, exhausted = false;
+    uint32_t rec = 0, slot = 0, skip = 0xFFFFFFFFu;
+    for (;;) {
+        unsigned idle = __ballot_sync(PATHS_FULL_MASK, !has);
+        int n = __popc(idle);
+        if (!exhausted && n >= MIN_REFILL) {
+            int leader = __ffs(idle) - 1;
+            uint32_t base = 0;
+            if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)n);
+            base = __shfl_sync(PATHS_FULL_MASK, base, leader);
+            if (!has) {
+                uint32_t i = base + __popc(idle & lt);
+                if (i < count) {
+                    rec = i;
+                    double4 o = ld_rec(&ps.sh_o[i]), d = ld_rec(&ps.sh_d[i]);
+                    uint32_t lid = real_to_bits(o.w);
+                    slot = real_to_bits(d.w);
+                    double t_light = (double)__int_as_float(0x7f800000);
+                    skip = 0xFFFFFFFFu;
+                    D3v so = mk3(o.x, o.y, o.z), sdir = mk3(d.x, d.y, d.z);
+                    if (lid != PATHS_LIGHT_ENV) { // nearest hit on the light's own sphere bounds the search (see k_shadow)
+                        const DevLight &l = sc.lights[lid];
+                        skip = l.prim;
+                        double tl;
+                        if (l.geometry == 1 && sphere_hit64(mk3(l.v[0], l.v[1], l.v[2]), l.radius, so, sdir, tl)) t_light = tl;
+                    }
+                    tv.init<true>(so, sdir, t_light, sc.fast_root);
+                    has = true;
+                }
+            }
+            exhausted = base + (uint32_t)n >= count;
+        }
+        if (!__any_sync(PATHS_FULL_MASK, has)) break;
+        if (has) {
+#pragma unroll 1
+            for (int k = 0; k < KI && tv.node >= 0; k++) tv.inner(nodes, stack);
+            bool occluded = false;
+            if (tv.node < 0 && tv.node != PATHS_TRAV_DONE) occluded = tv.leaf<true>(sc, leaves, stack, skip);
+            if (occluded) has = false;
+            else if (tv.node == PATHS_TRAV_DONE) { // trace.rs:81: colour += direct * throughput
+                double4 c = ld_rec(&ps.sh_c[rec]);
+                double4 col = ld_rec(&ps.col[slot]);
+                col.x += c.x; col.y += c.y; col.z += c.z;
+                if (!(col.x >= 0.0 && col.y >= 0.0 && col.z >= 0.0)) atomicAdd(totals + 2, 1ull); // Colour::check (trace.rs:82); NaN counts
+                st_rec(&ps.col[slot], col);
+                has = false;
             }
         }
     }

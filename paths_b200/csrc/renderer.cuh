@@ -85,6 +85,7 @@ struct TraceConfig {
     int variant = 3;    // bounce and visibility rays: 0 plain batches (k_extend / k_shadow), 3 two-wide lane refill, 16 four-wide
     int variant_b0 = 1; // camera segment: 1 = k_camera_extend (raygen fused with a plain-batch closest hit), 0/3/16 = k_raygen + that kernel
     int grid_trace = 0, grid_camera = 0, grid4 = 0, grid_camera4 = 0;
+    int grid_mixed = 0; // lane-refill kernels of mixed mode (f64 path state over the two-wide tree)
     bool camera_wide4 = false; // camera segment over the four-wide nodes (scenes above 64k primitives)
     size_t smem4 = 0;
 };
@@ -123,6 +124,8 @@ template <typename R> paths_status configure_trace(const SceneDevice *sd, TraceC
     if constexpr (IsF64<R>::value) {
         PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (k_extend<R, false>), 128, 0));
         tc.grid_trace = tc.sm_count * std::max(bps, 1);
+        PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (PATHS_K_EXTEND2M), 128, 0));
+        tc.grid_mixed = tc.sm_count * std::max(bps, 1);
         tc.variant = 0;
         tc.variant_b0 = 0;
     } else {

@@ -4,6 +4,9 @@
 
 #include "renderer.cuh"
 
+#ifndef PATHS_MIXED_REFILL
+#define PATHS_MIXED_REFILL 1 /* 0 = plain batches (k_extend / k_shadow), 1 = lane refill for bounce and visibility rays, 2 = camera rays too */
+#endif
 #ifndef PATHS_SHARD_TILE
 #define PATHS_SHARD_TILE 32u /* edge of the square image tiles dealt to the ranks under PATHS_SHARD_TILES */
 #endif
@@ -284,6 +287,13 @@ template <typename R> class RendererImpl : public RendererBase {
             default: break;
             }
         }
+        if constexpr (IsF64<R>::value) {
+            // mixed mode: lane refill for the bounce rays; the camera segment keeps plain batches (coherent rays, like k_camera_extend)
+            if (mixed_ && PATHS_MIXED_REFILL && (b > 0 || PATHS_MIXED_REFILL > 1)) {
+                PATHS_K_EXTEND2M<<<tc_.grid_mixed, 128, 0, cs_>>>(sd_->view, q, ps_.hit, pc_.qcount + b, pc_.work + PATHS_NWORK * b);
+                return;
+            }
+        }
         if (mixed_) k_extend<R, true><<<tc_.grid_trace, 128, 0, cs_>>>(sd_->view, q, ps_.hit, pc_.qcount + b, pc_.work + PATHS_NWORK * b);
         else k_extend<R, false><<<tc_.grid_trace, 128, 0, cs_>>>(sd_->view, q, ps_.hit, pc_.qcount + b, pc_.work + PATHS_NWORK * b);
     }
@@ -296,6 +306,12 @@ template <typename R> class RendererImpl : public RendererBase {
             }
             if (tc_.variant != 0) {
                 PATHS_K_SHADOW2<<<tc_.grid_trace, 128, 0, cs_>>>(sd_->view, ps, count, cursor, pc_.totals);
+                return;
+            }
+        }
+        if constexpr (IsF64<R>::value) {
+            if (mixed_ && PATHS_MIXED_REFILL) {
+                PATHS_K_SHADOW2M<<<tc_.grid_mixed, 128, 0, cs_>>>(sd_->view, ps, count, cursor, pc_.totals);
                 return;
             }
         }

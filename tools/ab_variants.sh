@@ -5,7 +5,7 @@ for round in $(seq 1 ${ROUNDS:-2}); do
   for s in $scenes; do
     for which in $variants; do
       d=$which; [ "$which" != "." ] && d=ab/$which
-      timeout 300 python $d/tools/quick_bench.py scenes/$s.yml $spp 2>&1 | tail -2 | python -c "
+      timeout 300 python $d/tools/quick_bench.py scenes/$s.yml $spp 1920 1080 ${PREC:-32} 2>&1 | tail -2 | python -c "
 import sys,json
 for ln in sys.stdin:
     try: d=json.loads(ln)
