@@ -270,8 +270,10 @@ uint32_t emit4(const std::vector<SNode> &sn, int node, FastTree &out, int32_t &c
 } // namespace
 
 bool build_fast_tree(const HostScene &s, FastTree &out, std::string &err) {
-    if (const char *v = getenv("PATHS_SAH_MAXLEAF")) kMaxLeaf = (uint32_t)std::min(8, std::max(1, atoi(v))); // development switches
+#ifdef PATHS_DEV_SWITCHES /* development builds only (make EXTRA=-DPATHS_DEV_SWITCHES): a stale variable must not change a release run */
+    if (const char *v = getenv("PATHS_SAH_MAXLEAF")) kMaxLeaf = (uint32_t)std::min(8, std::max(1, atoi(v)));
     if (const char *v = getenv("PATHS_SAH_PRIMCOST")) kPrimCost = (float)atof(v);
+#endif
     std::vector<Ref> refs;
     refs.reserve(s.prims.size());
     // The slab test evaluates lo * (1/d) - o * (1/d): its error is about one ulp of the ORIGIN's coordinate, wherever the box is.

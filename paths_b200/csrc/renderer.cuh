@@ -312,6 +312,22 @@ paths_status trace_closest_impl(const SceneDevice *sd, const double *o, const do
             staged = true;
         }
     }
+    if constexpr (IsF64<R>::value && MIXED) { // mixed mode: the lane-refill kernel a render launches for its bounce rays
+        TraceConfig tc;
+        paths_status st = configure_trace<R>(sd, tc, err);
+        if (st != PATHS_OK) return st;
+        PathState<R4> ps;
+        std::memset(&ps, 0, sizeof(ps));
+        PATHS_CU(mem.get(&ps.ray[0], 2 * n));
+        PATHS_CU(mem.get(&ps.hit, n));
+        PATHS_CU(mem.get(&ctl, 2));
+        const uint32_t host_ctl[2] = {(uint32_t)n, 0u}; // queue length, fetch cursor
+        PATHS_CU(cudaMemcpy(ctl, host_ctl, sizeof(host_ctl), cudaMemcpyHostToDevice));
+        k_stage_rays<R4><<<blocks, 128>>>(d_o, d_d, (uint32_t)n, ps.ray[0]);
+        PATHS_K_EXTEND2M<<<tc.grid_mixed, 128>>>(sd->view, ps.ray[0], ps.hit, ctl, ctl + 1);
+        k_unstage_hits<R4><<<blocks, 128>>>(ps.hit, sd->view, (uint32_t)n, d_p, d_t, d_b);
+        staged = true;
+    }
     if (!staged) {
         bool wide = false;
         if constexpr (!IsF64<R>::value) { // PATHS_TRACE_CAMERA: the routine the fused camera kernel runs for this scene
@@ -390,6 +406,10 @@ paths_status trace_occluded_impl(const SceneDevice *sd, const double *o, const d
             PATHS_K_SHADOW2<<<tc.grid_trace, 128>>>(sd->view, ps, ctl, ctl + 1, totals);
             launched = true;
         }
+    }
+    if constexpr (IsF64<R>::value && MIXED) {
+        PATHS_K_SHADOW2M<<<tc.grid_mixed, 128>>>(sd->view, ps, ctl, ctl + 1, totals);
+        launched = true;
     }
     if (!launched) k_shadow<R, MIXED><<<tc.grid_trace, 128>>>(sd->view, ps, ctl, ctl + 1, totals);
     k_unstage_shadow<R4><<<blocks, 128>>>(ps.col, (uint32_t)n, d_occ);
