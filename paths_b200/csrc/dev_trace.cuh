@@ -62,6 +62,16 @@ __device__ __forceinline__ bool prim_hit64(const DevScene &sc, uint32_t prim, D3
     return sphere_hit64(mk3(g[0], g[1], g[2]), g[3], o, d, t);
 }
 
+// the same test for a primitive met in a production-tree leaf: the leaf tag's top bit says "sphere" (bvh_fast.cpp), which saves the
+// dependent load of prim_meta on the traversal path
+__device__ __forceinline__ bool prim_hit64_tagged(const DevScene &sc, uint32_t tag, D3v o, D3v d, double &t, double &bx, double &by) {
+    const double *g = sc.prim_geom + (size_t)(tag & 0x7FFFFFFFu) * 12;
+    if (!(tag & 0x80000000u)) return triangle_hit64(g, o, d, t, bx, by);
+    bx = 0.0;
+    by = 0.0;
+    return sphere_hit64(mk3(g[0], g[1], g[2]), g[3], o, d, t);
+}
+
 // src/bvh.rs:8-21: strict tmin < tmax, optional tmin < len, no tmax >= 0 test; Rust f64::min/max ignore NaN like fmin/fmax
 __device__ __forceinline__ bool slab_ref(const double *box, D3v o, D3v inv, bool has_len, double len, double &tmin_out) {
     D3v t0 = (mk3(box[0], box[1], box[2]) - o) * inv;
@@ -386,11 +396,14 @@ template <bool ANY> __device__ __forceinline__ Hit64 trace_mixed(const DevScene 
         {
             uint32_t code = (uint32_t)~node;
             uint32_t first = code >> 3, cnt = (code & 7u) + 1u;
+            uint32_t tag_next = __float_as_uint(__ldg(leaves + 3 * first + 2).w);
             for (uint32_t k = 0; k < cnt; k++) {
-                uint32_t prim = __float_as_uint(__ldg(leaves + 3 * (first + k) + 2).w) & 0x7FFFFFFFu;
+                const uint32_t tag = tag_next;
+                if (k + 1 < cnt) tag_next = __float_as_uint(__ldg(leaves + 3 * (first + k + 1) + 2).w); // in flight during this test
+                uint32_t prim = tag & 0x7FFFFFFFu;
                 if (ANY && prim == skip_prim) continue;
                 double t, bx, by;
-                if (prim_hit64(sc, prim, o, d, t, bx, by)) {
+                if (prim_hit64_tagged(sc, tag, o, d, t, bx, by)) {
                     // src/bvh.rs:93-104: the first hit is taken as it is (even t = inf), later ones only when strictly closer
                     if (ANY ? t < best.t : (best.prim == 0xFFFFFFFFu || t < best.t)) {
                         best.prim = prim;
@@ -563,13 +576,25 @@ struct TravM {
     }
     // one leaf, then pop.  Returns true when ANY and a primitive other than skip_prim was hit closer than the bound.
     template <bool ANY> __device__ __forceinline__ bool leaf(const DevScene &sc, const float4 *__restrict__ leaves, int32_t *stack, uint32_t skip_prim) {
-        uint32_t code = (uint32_t)~node;
+        if (leaf_test<ANY>(sc, leaves, node, skip_prim)) return true;
+        node = sp > 0 ? stack[--sp] : PATHS_TRAV_DONE;
+        return false;
+    }
+    __device__ __forceinline__ int32_t pop(int32_t *stack) { return sp > 0 ? stack[--sp] : PATHS_TRAV_DONE; }
+    // tests the primitives of leaf `leaf_code` (< 0) without touching the traversal position.  A leaf may be tested later than it was
+    // reached (k_extend2s_m): boxes met meanwhile were tested against a bound that had not shrunk yet, which only adds visits -- every
+    // primitive in a box the fresh bound would have culled lies farther than the hit already held, and is turned down here.
+    template <bool ANY> __device__ __forceinline__ bool leaf_test(const DevScene &sc, const float4 *__restrict__ leaves, int32_t leaf_code, uint32_t skip_prim) {
+        uint32_t code = (uint32_t)~leaf_code;
         uint32_t first = code >> 3, cnt = (code & 7u) + 1u;
+        uint32_t tag_next = __float_as_uint(__ldg(leaves + 3 * first + 2).w);
         for (uint32_t k = 0; k < cnt; k++) {
-            uint32_t p = __float_as_uint(__ldg(leaves + 3 * (first + k) + 2).w) & 0x7FFFFFFFu;
+            const uint32_t tag = tag_next;
+            if (k + 1 < cnt) tag_next = __float_as_uint(__ldg(leaves + 3 * (first + k + 1) + 2).w); // in flight during this test
+            uint32_t p = tag & 0x7FFFFFFFu;
             if (ANY && p == skip_prim) continue;
             double tt, hx, hy;
-            if (prim_hit64(sc, p, o, d, tt, hx, hy)) {
+            if (prim_hit64_tagged(sc, tag, o, d, tt, hx, hy)) {
                 // src/bvh.rs:93-104: the first hit is taken as it is (even t = inf), later ones only when strictly closer
                 if (ANY ? tt < t : (prim == 0xFFFFFFFFu || tt < t)) {
                     prim = p; t = tt; bx = hx; by = hy;
@@ -578,7 +603,6 @@ struct TravM {
                 }
             }
         }
-        node = sp > 0 ? stack[--sp] : PATHS_TRAV_DONE;
         return false;
     }
 };

@@ -806,15 +806,25 @@ __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_shadow_refill(DevScene
 // The plain batches of k_extend<double, true> leave a warp waiting for its slowest ray (doom.yml at 1080p: 95 of 189 ms per 32 spp in
 // extend).  Same schedule as k_extend_refill over the f64 path state; every ray's answer is bit-identical to trace_mixed's.
 #ifndef PATHS_M2_MIN
-#define PATHS_M2_MIN 16
+#define PATHS_M2_MIN 8 /* refill as soon as 8 lanes idle: an f64 leaf is long, idle lanes cost more than in f32 (doom +1.8 % over 16; profiles/r02zz_mixed_refill_ab.txt) */
 #endif
 #ifndef PATHS_M2_KI
 #define PATHS_M2_KI 8
 #endif
+#ifndef PATHS_LB_M2
+#define PATHS_LB_M2 6
+#endif
+#ifndef PATHS_M2_SPEC
+#define PATHS_M2_SPEC 0 /* > 0: k_extend2s_m with this MIN_INNER (parked leaves) */
+#endif
+#if PATHS_M2_SPEC > 0
+#define PATHS_K_EXTEND2M k_extend2s_m<PATHS_M2_MIN, PATHS_M2_KI, PATHS_M2_SPEC>
+#else
 #define PATHS_K_EXTEND2M k_extend_refill_m<PATHS_M2_MIN, PATHS_M2_KI>
+#endif
 #define PATHS_K_SHADOW2M k_shadow_refill_m<PATHS_M2_MIN, PATHS_M2_KI>
 template <int MIN_REFILL, int KI>
-__global__ void __launch_bounds__(128) k_extend_refill_m(DevScene sc, const double4 *__restrict__ rays, double4 *__restrict__ hits,
+__global__ void __launch_bounds__(128, PATHS_LB_M2) k_extend_refill_m(DevScene sc, const double4 *__restrict__ rays, double4 *__restrict__ hits,
                                                          const uint32_t *count_ptr, uint32_t *cursor) {
     const uint32_t count = *count_ptr;
     const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
@@ -857,8 +867,74 @@ __global__ void __launch_bounds__(128) k_extend_refill_m(DevScene sc, const doub
     }
 }
 
+// Mixed mode, parked leaves: a lane that reaches a leaf parks it and keeps descending from its stack; the leaves are tested when fewer
+// than MIN_INNER lanes still have an inner node to visit, so that the long f64 primitive tests run with many lanes at once (ncu on
+// doom.yml bounce 1 with k_extend_refill_m: the triangle test ran at 7 of 32 lanes, the slab tests at 15).  Same answers (TravM::leaf_test).
+template <int MIN_REFILL, int KI, int MIN_INNER>
+__global__ void __launch_bounds__(128) k_extend2s_m(DevScene sc, const double4 *__restrict__ rays, double4 *__restrict__ hits,
+                                                    const uint32_t *count_ptr, uint32_t *cursor) {
+    const uint32_t count = *count_ptr;
+    const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    const float4 *__restrict__ nodes = sc.fast_nodes;
+    const float4 *__restrict__ leaves = sc.fast_leaves;
+    int32_t stack[PATHS_FAST_STACK];
+    TravM tv;
+    tv.node = PATHS_TRAV_DONE;
+    bool has = false, exhausted = false;
+    uint32_t slot = 0;
+    int32_t pend = 0;
+    for (;;) {
+        unsigned idle = __ballot_sync(PATHS_FULL_MASK, !has);
+        int n = __popc(idle);
+        if (!exhausted && n >= MIN_REFILL) {
+            int leader = __ffs(idle) - 1;
+            uint32_t base = 0;
+            if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)n);
+            base = __shfl_sync(PATHS_FULL_MASK, base, leader);
+            if (!has) {
+                uint32_t i = base + __popc(idle & lt);
+                if (i < count) {
+                    slot = i;
+                    double4 o = ld_rec(&rays[2 * (size_t)i]), d = ld_rec(&rays[2 * (size_t)i + 1]);
+                    tv.init<false>(mk3(o.x, o.y, o.z), mk3(d.x, d.y, d.z), (double)__int_as_float(0x7f800000), sc.fast_root);
+                    pend = 0;
+                    has = true;
+                }
+            }
+            exhausted = base + (uint32_t)n >= count;
+        }
+        const int n_has = __popc(__ballot_sync(PATHS_FULL_MASK, has));
+        if (n_has == 0) break;
+#pragma unroll 1
+        for (int k = 0; k < KI; k++) {
+            bool inner = has && tv.node >= 0;
+            int n_inner = __popc(__ballot_sync(PATHS_FULL_MASK, inner));
+            if (n_inner == 0 || (n_inner < MIN_INNER && n_inner < n_has)) break;
+            if (inner) tv.inner(nodes, stack);
+            if (has && pend == 0 && tv.node < 0 && tv.node != PATHS_TRAV_DONE) {
+                pend = tv.node;
+                tv.node = tv.pop(stack);
+            }
+        }
+        if (has) {
+            if (pend == 0 && tv.node < 0 && tv.node != PATHS_TRAV_DONE) { // reached while the inner phase was cut short
+                pend = tv.node;
+                tv.node = tv.pop(stack);
+            }
+            if (pend != 0) {
+                tv.leaf_test<false>(sc, leaves, pend, 0xFFFFFFFFu);
+                pend = 0;
+            }
+            if (tv.node == PATHS_TRAV_DONE) {
+                st_rec(&hits[slot], mk4(bits_to_real(tv.prim, 0.0), tv.t, tv.bx, tv.by));
+                has = false;
+            }
+        }
+    }
+}
+
 template <int MIN_REFILL, int KI>
-__global__ void __launch_bounds__(128) k_shadow_refill_m(DevScene sc, PathState<double4> ps, const uint32_t *count_ptr, uint32_t *cursor,
+__global__ void __launch_bounds__(128, PATHS_LB_M2) k_shadow_refill_m(DevScene sc, PathState<double4> ps, const uint32_t *count_ptr, uint32_t *cursor,
                                                          unsigned long long *totals) {
     const uint32_t count = *count_ptr;
     const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
