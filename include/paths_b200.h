@@ -228,7 +228,7 @@ paths_status paths_scene_prim_entity(const paths_scene *s, uint32_t prim, int32_
 /* BVH::find_intersection over a batch of host rays (src/bvh.rs:78-140).  prim_id = PATHS_MISS and t = +inf on a miss.
  * precision 64: reference-order binary tree, f64, reference operation order (bit-exact ids and t);
  * precision 48: production tree, f32 box tests, the reference's f64 primitive tests (mixed mode), through the lane-refill kernel a
- *   mixed-precision render launches for its bounce rays (k_extend_refill_m);
+ *   mixed-precision render launches for its bounce rays (k_extend_refill_m, k_extend4_m above 64k primitives);
  * precision 32: the PRODUCTION closest-hit kernel: the rays are staged into a path-state buffer and traced by the very kernel, node
  *   layout and grid a render of this scene launches for its bounce rays (k_extend_refill over two-wide nodes up to 64k primitives,
  *   k_extend4s over four-wide nodes above); f32 boxes and watertight f32 triangles, f64 spheres;
@@ -239,7 +239,7 @@ paths_status paths_trace_closest(paths_scene *s, int32_t device, const double *o
                                  uint32_t *prim_id, double *t, double *bary, int32_t precision);
 /* The shadow query of trace_ray (src/trace.rs:61-66: closest hit, then `entity != light`) over a batch of host rays, through the
  * visibility kernel a render launches (precision 32: k_shadow_refill / k_shadow4 -- any-hit with the nearest hit on the light's own
- * sphere as the search bound; 48: the same predicate with f64 primitives (k_shadow_refill_m); 64: the reference's closest-hit-then-compare rule on its
+ * sphere as the search bound; 48: the same predicate with f64 primitives (k_shadow_refill_m / k_shadow4_m); 64: the reference's closest-hit-then-compare rule on its
  * own tree; PATHS_TRACE_* codes as above).  light[i] = index of the light ray i was sampled toward (hits on that light do not
  * occlude), or NULL: every hit occludes.  occluded[i] = 1 blocked, 0 clear (the kernel added the record's contribution to its path's
  * radiance exactly once). */

@@ -671,6 +671,64 @@ struct TravF4 : TravF {
 };
 
 
+// Mixed mode over the four-wide nodes (scenes above 64k primitives): the slab tests of TravF4 against TravM's f32 bound, the f64
+// primitive tests of TravM at the leaves, stack in shared memory.  Half as many dependent node fetches per ray as the two-wide walk,
+// which is what a kernel that waits on memory wants.  Visiting order differs from trace_mixed's, so exact-t ties may resolve to
+// another primitive; the closest distance does not depend on the tree.
+struct TravM4 : TravM {
+    template <bool SORT = true> __device__ __forceinline__ void inner4(const float4 *__restrict__ nodes4, int32_t *sstack, uint32_t stride) {
+        const float4 *n = nodes4 + 8 * (size_t)node;
+        const float4 lox = __ldg(n), hix = __ldg(n + 1), loy = __ldg(n + 2), hiy = __ldg(n + 3), loz = __ldg(n + 4), hiz = __ldg(n + 5);
+        const float4 chf = __ldg(n + 6);
+        const float inf = __int_as_float(0x7f800000);
+        float k0, k1, k2, k3;
+#define PATHS_BOX4M(c, key)                                                                                                 \
+    {                                                                                                                       \
+        float x0 = __fmaf_rn(lox.c, idx, oix), x1 = __fmaf_rn(hix.c, idx, oix), y0 = __fmaf_rn(loy.c, idy, oiy);            \
+        float y1 = __fmaf_rn(hiy.c, idy, oiy), z0 = __fmaf_rn(loz.c, idz, oiz), z1 = __fmaf_rn(hiz.c, idz, oiz);            \
+        float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.0f));                                  \
+        float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), tbound)) * 1.0000004f;                   \
+        key = tn <= tf ? tn : inf;                                                                                          \
+    }
+        PATHS_BOX4M(x, k0)
+        PATHS_BOX4M(y, k1)
+        PATHS_BOX4M(z, k2)
+        PATHS_BOX4M(w, k3)
+#undef PATHS_BOX4M
+        int32_t c0 = __float_as_int(chf.x), c1 = __float_as_int(chf.y), c2 = __float_as_int(chf.z), c3 = __float_as_int(chf.w);
+        k0 = c0 == PATHS_CHILD_EMPTY ? inf : k0;
+        k1 = c1 == PATHS_CHILD_EMPTY ? inf : k1;
+        k2 = c2 == PATHS_CHILD_EMPTY ? inf : k2;
+        k3 = c3 == PATHS_CHILD_EMPTY ? inf : k3;
+#define PATHS_CE(ka, ca, kb, cb)          \
+    if (kb < ka) {                        \
+        float tk = ka; ka = kb; kb = tk;  \
+        int32_t tc = ca; ca = cb; cb = tc;\
+    }
+        if (SORT) {
+            PATHS_CE(k0, c0, k1, c1)
+            PATHS_CE(k2, c2, k3, c3)
+            PATHS_CE(k0, c0, k2, c2)
+            PATHS_CE(k1, c1, k3, c3)
+            PATHS_CE(k1, c1, k2, c2)
+            if (k3 < inf) sstack[(sp++) * stride] = c3;
+            if (k2 < inf) sstack[(sp++) * stride] = c2;
+            if (k1 < inf) sstack[(sp++) * stride] = c1;
+            if (k0 < inf) node = c0;
+            else node = sp > 0 ? sstack[(--sp) * stride] : PATHS_TRAV_DONE;
+        } else {
+            int32_t next = PATHS_TRAV_DONE;
+            if (k0 < inf) next = c0;
+            if (k1 < inf) { if (next != PATHS_TRAV_DONE) sstack[(sp++) * stride] = next; next = c1; }
+            if (k2 < inf) { if (next != PATHS_TRAV_DONE) sstack[(sp++) * stride] = next; next = c2; }
+            if (k3 < inf) { if (next != PATHS_TRAV_DONE) sstack[(sp++) * stride] = next; next = c3; }
+            node = next != PATHS_TRAV_DONE ? next : (sp > 0 ? sstack[(--sp) * stride] : PATHS_TRAV_DONE);
+        }
+#undef PATHS_CE
+    }
+    __device__ __forceinline__ int32_t pop4(const int32_t *sstack, uint32_t stride) { return sp > 0 ? sstack[(--sp) * stride] : PATHS_TRAV_DONE; }
+};
+
 // plain per-lane closest hit over the four-wide nodes (camera segment of large scenes, and the per-ray seam that tests it)
 __device__ __forceinline__ HitF trace_plain4(const DevScene &sc, float ox, float oy, float oz, float dx, float dy, float dz, int32_t *sstack,
                                              uint32_t stride) {

@@ -994,6 +994,128 @@ __global__ void __launch_bounds__(128, PATHS_LB_M2) k_shadow_refill_m(DevScene s
     }
 }
 
+// Mixed mode over the four-wide nodes (scenes above 64k primitives, like the f32 path): lane refill, stack of 3 * depth + 1 levels per
+// thread in dynamic shared memory.  Leaves are tested where they are met (parking them lost in the two-wide mixed kernel).
+#ifndef PATHS_M4_KI
+#define PATHS_M4_KI 4
+#endif
+#define PATHS_K_EXTEND4M k_extend4_m<PATHS_M2_MIN, PATHS_M4_KI>
+#define PATHS_K_SHADOW4M k_shadow4_m<PATHS_M2_MIN, PATHS_M4_KI>
+template <int MIN_REFILL, int KI>
+__global__ void __launch_bounds__(128, PATHS_LB_M2) k_extend4_m(DevScene sc, const double4 *__restrict__ rays, double4 *__restrict__ hits,
+                                                                  const uint32_t *count_ptr, uint32_t *cursor) {
+    extern __shared__ int32_t smem_stack[];
+    int32_t *sstack = smem_stack + threadIdx.x;
+    const uint32_t stride = blockDim.x;
+    const uint32_t count = *count_ptr;
+    const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    const float4 *__restrict__ nodes4 = sc.fast4_nodes;
+    const float4 *__restrict__ leaves = sc.fast_leaves;
+    TravM4 tv;
+    tv.node = PATHS_TRAV_DONE;
+    bool has = false, exhausted = false;
+    uint32_t slot = 0;
+    for (;;) {
+        unsigned idle = __ballot_sync(PATHS_FULL_MASK, !has);
+        int n = __popc(idle);
+        if (!exhausted && n >= MIN_REFILL) {
+            int leader = __ffs(idle) - 1;
+            uint32_t base = 0;
+            if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)n);
+            base = __shfl_sync(PATHS_FULL_MASK, base, leader);
+            if (!has) {
+                uint32_t i = base + __popc(idle & lt);
+                if (i < count) {
+                    slot = i;
+                    double4 o = ld_rec(&rays[2 * (size_t)i]), d = ld_rec(&rays[2 * (size_t)i + 1]);
+                    tv.init<false>(mk3(o.x, o.y, o.z), mk3(d.x, d.y, d.z), (double)__int_as_float(0x7f800000), sc.fast4_root);
+                    has = true;
+                }
+            }
+            exhausted = base + (uint32_t)n >= count;
+        }
+        if (!__any_sync(PATHS_FULL_MASK, has)) break;
+        if (has) {
+#pragma unroll 1
+            for (int k = 0; k < KI && tv.node >= 0; k++) tv.inner4<true>(nodes4, sstack, stride);
+            if (tv.node < 0 && tv.node != PATHS_TRAV_DONE) {
+                tv.leaf_test<false>(sc, leaves, tv.node, 0xFFFFFFFFu);
+                tv.node = tv.pop4(sstack, stride);
+            }
+            if (tv.node == PATHS_TRAV_DONE) {
+                st_rec(&hits[slot], mk4(bits_to_real(tv.prim, 0.0), tv.t, tv.bx, tv.by));
+                has = false;
+            }
+        }
+    }
+}
+
+template <int MIN_REFILL, int KI>
+__global__ void __launch_bounds__(128, PATHS_LB_M2) k_shadow4_m(DevScene sc, PathState<double4> ps, const uint32_t *count_ptr, uint32_t *cursor,
+                                                                  unsigned long long *totals) {
+    extern __shared__ int32_t smem_stack[];
+    int32_t *sstack = smem_stack + threadIdx.x;
+    const uint32_t stride = blockDim.x;
+    const uint32_t count = *count_ptr;
+    const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    const float4 *__restrict__ nodes4 = sc.fast4_nodes;
+    const float4 *__restrict__ leaves = sc.fast_leaves;
+    TravM4 tv;
+    tv.node = PATHS_TRAV_DONE;
+    bool has = false, exhausted = false;
+    uint32_t rec = 0, slot = 0, skip = 0xFFFFFFFFu;
+    for (;;) {
+        unsigned idle = __ballot_sync(PATHS_FULL_MASK, !has);
+        int n = __popc(idle);
+        if (!exhausted && n >= MIN_REFILL) {
+            int leader = __ffs(idle) - 1;
+            uint32_t base = 0;
+            if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)n);
+            base = __shfl_sync(PATHS_FULL_MASK, base, leader);
+            if (!has) {
+                uint32_t i = base + __popc(idle & lt);
+                if (i < count) {
+                    rec = i;
+                    double4 o = ld_rec(&ps.sh_o[i]), d = ld_rec(&ps.sh_d[i]);
+                    uint32_t lid = real_to_bits(o.w);
+                    slot = real_to_bits(d.w);
+                    double t_light = (double)__int_as_float(0x7f800000);
+                    skip = 0xFFFFFFFFu;
+                    D3v so = mk3(o.x, o.y, o.z), sdir = mk3(d.x, d.y, d.z);
+                    if (lid != PATHS_LIGHT_ENV) { // nearest hit on the light's own sphere bounds the search (see k_shadow)
+                        const DevLight &l = sc.lights[lid];
+                        skip = l.prim;
+                        double tl;
+                        if (l.geometry == 1 && sphere_hit64(mk3(l.v[0], l.v[1], l.v[2]), l.radius, so, sdir, tl)) t_light = tl;
+                    }
+                    tv.init<true>(so, sdir, t_light, sc.fast4_root);
+                    has = true;
+                }
+            }
+            exhausted = base + (uint32_t)n >= count;
+        }
+        if (!__any_sync(PATHS_FULL_MASK, has)) break;
+        if (has) {
+#pragma unroll 1
+            for (int k = 0; k < KI && tv.node >= 0; k++) tv.inner4<false>(nodes4, sstack, stride);
+            bool occluded = false;
+            if (tv.node < 0 && tv.node != PATHS_TRAV_DONE) {
+                occluded = tv.leaf_test<true>(sc, leaves, tv.node, skip);
+                if (!occluded) tv.node = tv.pop4(sstack, stride);
+            }
+            if (occluded) has = false;
+            else if (tv.node == PATHS_TRAV_DONE) { // trace.rs:81: colour += direct * throughput
+                double4 c = ld_rec(&ps.sh_c[rec]);
+                double4 col = ld_rec(&ps.col[slot]);
+                col.x += c.x; col.y += c.y; col.z += c.z;
+                if (!(col.x >= 0.0 && col.y >= 0.0 && col.z >= 0.0)) atomicAdd(totals + 2, 1ull); // Colour::check (trace.rs:82); NaN counts
+                st_rec(&ps.col[slot], col);
+                has = false;
+            }
+        }
+    }
+}
+
 // ------------------------------------------------------------------ four-wide extend / shadow (lane refill, shared-memory stack)
 template <int ROUNDS, int MIN_REFILL, int KI>
 __global__ void __launch_bounds__(128, PATHS_LB_EXTEND) k_shadow4(DevScene sc, PathState<float4> ps, const uint32_t *count_ptr, uint32_t *cursor,

@@ -80,12 +80,16 @@ template <typename R> __global__ void k_add_sums(typename Vec4T<R>::type *sums, 
 // ------------------------------------------------------------------ which traversal kernels a scene runs on
 // ONE selection shared by RendererImpl (the render) and the per-ray seam (paths_trace_closest / paths_trace_occluded with precision
 // 32), so that a fixed-ray test drives exactly the kernels, node layout and grids a render of the same scene launches.
+#ifndef PATHS_MIXED_WIDE4
+#define PATHS_MIXED_WIDE4 1 /* mixed mode: four-wide nodes for bounce and visibility rays of scenes above 64k primitives */
+#endif
 struct TraceConfig {
     int sm_count = 148;
     int variant = 3;    // bounce and visibility rays: 0 plain batches (k_extend / k_shadow), 3 two-wide lane refill, 16 four-wide
     int variant_b0 = 1; // camera segment: 1 = k_camera_extend (raygen fused with a plain-batch closest hit), 0/3/16 = k_raygen + that kernel
     int grid_trace = 0, grid_camera = 0, grid4 = 0, grid_camera4 = 0;
     int grid_mixed = 0; // lane-refill kernels of mixed mode (f64 path state over the two-wide tree)
+    int grid_mixed4 = 0; // the same over the four-wide nodes (scenes above 64k primitives); 0 = not available
     bool camera_wide4 = false; // camera segment over the four-wide nodes (scenes above 64k primitives)
     size_t smem4 = 0;
 };
@@ -126,6 +130,14 @@ template <typename R> paths_status configure_trace(const SceneDevice *sd, TraceC
         tc.grid_trace = tc.sm_count * std::max(bps, 1);
         PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (PATHS_K_EXTEND2M), 128, 0));
         tc.grid_mixed = tc.sm_count * std::max(bps, 1);
+        // mixed mode over the four-wide nodes: same size rule and shared-memory stack as the f32 kernels
+        tc.smem4 = (size_t)(3 * sd->view.fast4_depth + 1) * 128 * sizeof(int32_t);
+        if (PATHS_MIXED_WIDE4 && sd->view.n_prims > 65536u && sd->view.fast4_nodes && tc.smem4 <= 200 * 1024) {
+            PATHS_CU(cudaFuncSetAttribute(PATHS_K_EXTEND4M, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc.smem4));
+            PATHS_CU(cudaFuncSetAttribute(PATHS_K_SHADOW4M, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc.smem4));
+            PATHS_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, PATHS_K_EXTEND4M, 128, tc.smem4));
+            tc.grid_mixed4 = tc.sm_count * std::max(bps, 1);
+        } else tc.smem4 = 0;
         tc.variant = 0;
         tc.variant_b0 = 0;
     } else {
@@ -324,7 +336,8 @@ paths_status trace_closest_impl(const SceneDevice *sd, const double *o, const do
         const uint32_t host_ctl[2] = {(uint32_t)n, 0u}; // queue length, fetch cursor
         PATHS_CU(cudaMemcpy(ctl, host_ctl, sizeof(host_ctl), cudaMemcpyHostToDevice));
         k_stage_rays<R4><<<blocks, 128>>>(d_o, d_d, (uint32_t)n, ps.ray[0]);
-        PATHS_K_EXTEND2M<<<tc.grid_mixed, 128>>>(sd->view, ps.ray[0], ps.hit, ctl, ctl + 1);
+        if (tc.grid_mixed4 > 0) PATHS_K_EXTEND4M<<<tc.grid_mixed4, 128, tc.smem4>>>(sd->view, ps.ray[0], ps.hit, ctl, ctl + 1);
+        else PATHS_K_EXTEND2M<<<tc.grid_mixed, 128>>>(sd->view, ps.ray[0], ps.hit, ctl, ctl + 1);
         k_unstage_hits<R4><<<blocks, 128>>>(ps.hit, sd->view, (uint32_t)n, d_p, d_t, d_b);
         staged = true;
     }
@@ -408,7 +421,8 @@ paths_status trace_occluded_impl(const SceneDevice *sd, const double *o, const d
         }
     }
     if constexpr (IsF64<R>::value && MIXED) {
-        PATHS_K_SHADOW2M<<<tc.grid_mixed, 128>>>(sd->view, ps, ctl, ctl + 1, totals);
+        if (tc.grid_mixed4 > 0) PATHS_K_SHADOW4M<<<tc.grid_mixed4, 128, tc.smem4>>>(sd->view, ps, ctl, ctl + 1, totals);
+        else PATHS_K_SHADOW2M<<<tc.grid_mixed, 128>>>(sd->view, ps, ctl, ctl + 1, totals);
         launched = true;
     }
     if (!launched) k_shadow<R, MIXED><<<tc.grid_trace, 128>>>(sd->view, ps, ctl, ctl + 1, totals);

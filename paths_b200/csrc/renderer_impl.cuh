@@ -290,7 +290,9 @@ template <typename R> class RendererImpl : public RendererBase {
         if constexpr (IsF64<R>::value) {
             // mixed mode: lane refill for the bounce rays; the camera segment keeps plain batches (coherent rays, like k_camera_extend)
             if (mixed_ && PATHS_MIXED_REFILL && (b > 0 || PATHS_MIXED_REFILL > 1)) {
-                PATHS_K_EXTEND2M<<<tc_.grid_mixed, 128, 0, cs_>>>(sd_->view, q, ps_.hit, pc_.qcount + b, pc_.work + PATHS_NWORK * b);
+                if (tc_.grid_mixed4 > 0)
+                    PATHS_K_EXTEND4M<<<tc_.grid_mixed4, 128, tc_.smem4, cs_>>>(sd_->view, q, ps_.hit, pc_.qcount + b, pc_.work + PATHS_NWORK * b);
+                else PATHS_K_EXTEND2M<<<tc_.grid_mixed, 128, 0, cs_>>>(sd_->view, q, ps_.hit, pc_.qcount + b, pc_.work + PATHS_NWORK * b);
                 return;
             }
         }
@@ -311,7 +313,8 @@ template <typename R> class RendererImpl : public RendererBase {
         }
         if constexpr (IsF64<R>::value) {
             if (mixed_ && PATHS_MIXED_REFILL) {
-                PATHS_K_SHADOW2M<<<tc_.grid_mixed, 128, 0, cs_>>>(sd_->view, ps, count, cursor, pc_.totals);
+                if (tc_.grid_mixed4 > 0) PATHS_K_SHADOW4M<<<tc_.grid_mixed4, 128, tc_.smem4, cs_>>>(sd_->view, ps, count, cursor, pc_.totals);
+                else PATHS_K_SHADOW2M<<<tc_.grid_mixed, 128, 0, cs_>>>(sd_->view, ps, count, cursor, pc_.totals);
                 return;
             }
         }
