@@ -29,8 +29,6 @@ from pathlib import Path
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 os.chdir(ROOT)
-# stdout carries ONE JSON line: NCCL's own banner ("NCCL version ...", printed when the box sets NCCL_DEBUG) goes to stderr
-os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 
 SCENES = {
     "teapot": ("scenes/teapot.yml", 1920, 1080),
