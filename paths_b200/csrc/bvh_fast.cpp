@@ -6,6 +6,7 @@
 // holds a 1e6-radius "plane" sphere (src/bvh.rs:178-182).  One reference behaviour does depend on the boxes and is kept:
 // a primitive whose own AABB is flat along an axis can never pass the strict `tmin < tmax` slab test of its leaf
 // (src/bvh.rs:16) and is therefore invisible; such primitives are left out of this tree.
+#include <cstdio>
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
@@ -60,7 +61,13 @@ struct SNode {
     uint32_t first, count; // leaf iff count > 0
 };
 
-const int kBins = 16;
+#ifndef PATHS_SAH_BINS
+#define PATHS_SAH_BINS 64 /* with the giants out of the build: 8 / 16 / 64 bins within +-0.7 % of each other, 64 ahead on teapot, bunny and dragon (profiles/r02zz_sah_giants_ab.txt) */
+#endif
+const int kBins = PATHS_SAH_BINS;
+#ifndef PATHS_SAH_GIANTS
+#define PATHS_SAH_GIANTS 1
+#endif
 uint32_t kMaxLeaf = 4;
 float kTraversalCost = 1.0f, kPrimCost = 1.2f;
 
@@ -336,9 +343,81 @@ bool build_fast_tree(const HostScene &s, FastTree &out, std::string &err) {
         (void)err;
         return true;
     }
+    // Giant primitives (the scenes' 1e6-radius "plane" spheres: extent above 1024 x the geometric mean extent, the device builder's rule,
+    // bvh_device.cu) are kept out of the SAH build and chained above its root.  Every ray is inside their boxes and tests them anyway;
+    // left in the build, their centroids stretch the binning domain until all ordinary primitives share one bin, and a giant can end up
+    // deep inside the mesh's subtree, where every node on its path inherits its box (bunny.yml, 16 bins: three levels of 3e6-wide nodes
+    // inside the mesh; closest-hit time 24.0 -> 20.3 ms per 64 spp once the giants sit at the top, profiles/r02zz_sah_bins_ab.txt).
+    size_t n_ord = refs.size();
+    if (PATHS_SAH_GIANTS && refs.size() > 1) {
+        double log_sum = 0.0;
+        std::vector<float> ext_of(refs.size());
+        for (size_t i = 0; i < refs.size(); i++) {
+            const FBox &b = refs[i].box;
+            ext_of[i] = std::max({b.hi[0] - b.lo[0], b.hi[1] - b.lo[1], b.hi[2] - b.lo[2]});
+            log_sum += std::log(std::max((double)ext_of[i], 1e-30));
+        }
+        const double threshold = 1024.0 * std::exp(log_sum / (double)refs.size());
+        std::vector<Ref> ord, giants;
+        for (size_t i = 0; i < refs.size(); i++) ((double)ext_of[i] > threshold ? giants : ord).push_back(refs[i]);
+        if (!giants.empty() && !ord.empty() && giants.size() <= 48) {
+            n_ord = ord.size();
+            refs = ord;
+            refs.insert(refs.end(), giants.begin(), giants.end()); // leaf slots of the giants follow the ordinary primitives'
+        }
+    }
     std::vector<SNode> sn;
     sn.reserve(refs.size());
-    int root = Sah::build(refs, 0, refs.size(), sn, 0);
+    int root = Sah::build(refs, 0, n_ord, sn, 0);
+    for (size_t g = n_ord; g < refs.size(); g++) { // chain: new root = {giant leaf, previous root}
+        SNode leaf;
+        leaf.box = refs[g].box;
+        leaf.left = leaf.right = -1;
+        leaf.first = (uint32_t)g;
+        leaf.count = 1;
+        int li = (int)sn.size();
+        sn.push_back(leaf);
+        SNode up;
+        up.box = refs[g].box;
+        up.box.grow(sn[root].box);
+        up.left = li; // the giant first (equal entry distances go left); searching the ordinary geometry first measured the same
+        up.right = root;
+        up.first = 0;
+        up.count = 0;
+        root = (int)sn.size();
+        sn.push_back(up);
+    }
+#ifdef PATHS_DEV_SWITCHES
+    if (getenv("PATHS_SAH_REPORT")) { // SAH cost of the binary tree, nodes holding a giant primitive (extent > 1e5) left out
+        double inner = 0.0, leaf = 0.0, amax = 0.0;
+        size_t n_inner = 0, n_leaf = 0;
+        for (const SNode &n : sn) {
+            float e = std::max({n.box.hi[0] - n.box.lo[0], n.box.hi[1] - n.box.lo[1], n.box.hi[2] - n.box.lo[2]});
+            if (!(e < 1e5f)) continue;
+            double a = n.box.half_area();
+            amax = std::max(amax, a);
+            if (n.count == 0) { inner += a; n_inner++; }
+            else { leaf += a * n.count; n_leaf++; }
+        }
+        if (atoi(getenv("PATHS_SAH_REPORT")) > 1) { // the top of the tree: where the giant primitives sit
+            struct Item { int node, depth; };
+            std::vector<Item> todo{{root, 0}};
+            while (!todo.empty()) {
+                Item it = todo.back();
+                todo.pop_back();
+                const SNode &n = sn[it.node];
+                float e = std::max({n.box.hi[0] - n.box.lo[0], n.box.hi[1] - n.box.lo[1], n.box.hi[2] - n.box.lo[2]});
+                size_t np = 0;
+                std::vector<int> st{it.node};
+                while (!st.empty()) { int k = st.back(); st.pop_back(); if (sn[k].count) np += sn[k].count; else { st.push_back(sn[k].left); st.push_back(sn[k].right); } }
+                fprintf(stderr, "[top] %*s node %d extent %.4g prims %zu %s\n", 2 * it.depth, "", it.node, e, np, n.count ? "LEAF" : "");
+                if (n.count == 0 && it.depth < 5 && (e > 1e5f || it.depth < 2)) { todo.push_back({n.right, it.depth + 1}); todo.push_back({n.left, it.depth + 1}); }
+            }
+        }
+        fprintf(stderr, "[sah] bins %d prims %zu inner %zu leaves %zu area_max %.6g cost_inner %.6g cost_leaf %.6g total(1.0,1.2) %.6g\n", kBins,
+                refs.size(), n_inner, n_leaf, amax, inner, leaf, kTraversalCost * inner + kPrimCost * leaf);
+    }
+#endif
     out.leaf_prims.resize(refs.size());
     for (size_t i = 0; i < refs.size(); i++) out.leaf_prims[i] = refs[i].prim;
     out.nodes.reserve(refs.size());
