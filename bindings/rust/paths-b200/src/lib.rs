@@ -46,6 +46,14 @@ impl Scene {
                                                  prim.as_mut_ptr(), t.as_mut_ptr(), ptr::null_mut(), precision) })?;
         Ok((prim, t))
     }
+    /// The f32 production closest hit with no device allocation (scratch in a static device array of the library): at most
+    /// `PATHS_STATIC_MAX_RAYS` rays per call, and the scene must already be staged on the device (any earlier query or renderer).
+    /// No counterpart in the reference.  The caller's output slices are filled in place: nothing is allocated on the host either.
+    pub fn find_intersection_static(&self, origins: &[[f64; 3]], dirs: &[[f64; 3]], prim: &mut [u32], t: &mut [f64]) -> Result<(), Error> {
+        assert!(origins.len() == dirs.len() && prim.len() == origins.len() && t.len() == origins.len());
+        check(unsafe { sys::paths_trace_closest_static(self.raw, 0, origins.as_ptr() as *const f64, dirs.as_ptr() as *const f64, origins.len(),
+                                                        prim.as_mut_ptr(), t.as_mut_ptr(), ptr::null_mut()) })
+    }
 }
 impl Drop for Scene { fn drop(&mut self) { unsafe { sys::paths_scene_destroy(self.raw) } } }
 
