@@ -29,6 +29,9 @@ call('paths_scene_get_info', None, C.byref(info))
 call('paths_scene_prim_geometry', None, 0, buf, C.byref(i32))
 call('paths_scene_prim_entity', None, 0, C.byref(i32), C.byref(u32), C.byref(u32))
 call('paths_trace_closest', None, 0, buf, buf, C.c_size_t(1), C.byref(u32), buf, None, 64)
+call('paths_trace_closest_static', None, 0, buf, buf, C.c_size_t(1), C.byref(u32), buf, None)
+u8 = C.c_uint8()
+call('paths_trace_occluded', None, 0, buf, buf, None, C.c_size_t(1), C.byref(u8), 32)
 L.paths_render_opts_default.restype = None; L.paths_render_opts_default(None)
 call('paths_renderer_create', None, C.byref(cam), C.byref(opts), C.byref(h))
 for name in ('paths_renderer_sync', 'paths_renderer_reset', 'paths_renderer_render_preview'):
@@ -54,6 +57,10 @@ call('paths_scene_build_bvh', s, 99)
 call('paths_trace_closest', s, 0, None, buf, C.c_size_t(1), C.byref(u32), buf, None, 64)
 call('paths_trace_closest', s, 0, buf, buf, C.c_size_t(1), None, buf, None, 64)
 call('paths_trace_closest', s, 0, buf, buf, C.c_size_t(1), C.byref(u32), buf, None, 17)
+call('paths_trace_closest_static', s, 0, None, buf, C.c_size_t(1), C.byref(u32), buf, None)
+call('paths_trace_closest_static', s, 0, buf, buf, C.c_size_t(1), C.byref(u32), None, None)
+call('paths_trace_closest_static', s, 0, buf, buf, C.c_size_t(1), C.byref(u32), buf, None)  # no device here / scene not staged: refused either way
+call('paths_trace_occluded', s, 0, buf, buf, None, C.c_size_t(1), None, 32)
 call('paths_renderer_create', s, None, C.byref(opts), C.byref(h))
 call('paths_renderer_create', s, C.byref(cam), C.byref(opts), None)
 print("UNEXPECTED OK:", bad)
