@@ -188,7 +188,8 @@ typedef struct {
     double build_ms_device;     /* CUDA-event time of the last device build */
     uint32_t bvh_builder;       /* builder of the production tree staged last: 0 host SAH, 1 device morton (LBVH) */
     uint32_t device_nodes2, device_nodes4, device_depth2, device_depth4;
-    uint32_t giant_prims;       /* primitives chained above the morton root (the scenes' 1e6-radius plane spheres) */
+    uint32_t giant_prims;       /* primitives chained above the root of the builder used last (the scenes' 1e6-radius plane spheres):
+                                 * extent above 1024 x the geometric mean extent, at most 48; both builders apply the rule */
 } paths_scene_info;
 
 /* ------------------------------------------------------------------ scene (replaces SceneDescription::scene + Scene::new,

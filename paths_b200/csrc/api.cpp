@@ -533,7 +533,7 @@ paths_status paths_scene_get_info(const paths_scene *s, paths_scene_info *info) 
     info->device_nodes4 = s->dev_info.nodes4;
     info->device_depth2 = s->dev_info.depth2;
     info->device_depth4 = s->dev_info.depth4;
-    info->giant_prims = s->dev_info.giants;
+    info->giant_prims = (s->last_builder == 0 && s->has_fast) ? s->fast.n_giants : s->dev_info.giants;
     return PATHS_OK;
 }
 

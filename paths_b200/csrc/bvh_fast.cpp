@@ -423,6 +423,7 @@ bool build_fast_tree(const HostScene &s, FastTree &out, std::string &err) {
                 refs.size(), n_inner, n_leaf, amax, inner, leaf, kTraversalCost * inner + kPrimCost * leaf);
     }
 #endif
+    out.n_giants = (uint32_t)(refs.size() - n_ord);
     out.leaf_prims.resize(refs.size());
     for (size_t i = 0; i < refs.size(); i++) out.leaf_prims[i] = refs[i].prim;
     out.nodes.reserve(refs.size());

@@ -112,6 +112,7 @@ struct FastTree {
     float root_box[6];
     std::vector<uint32_t> leaf_prims; // prim ids in leaf order
     uint32_t depth = 0;
+    uint32_t n_giants = 0; // primitives kept out of the SAH build and chained above its root (bvh_fast.cpp)
     // the same tree collapsed to four-wide nodes (every other level of the binary tree is folded into its parent)
     std::vector<FastNode4> nodes4;
     int32_t root4 = 0;

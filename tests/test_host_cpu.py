@@ -290,3 +290,30 @@ def test_rust_binding_declares_every_symbol():
         body = re.sub(r"//.*", "", body)
         fields = re.findall(r"pub\s+(\w+)\s*:", body)
         assert [f.rstrip("_") for f in fields] == [n for n, _ in ct._fields_], rust_name
+
+
+@pytest.mark.parametrize("name,giants", [("teapot", 1), ("bunny", 2), ("spheres_on_plane", 1), ("bokeh_demo", 1), ("teapot_light", 1)])
+def test_host_builder_chains_giant_primitives_above_the_root(pb, name, giants):
+    # The scenes' planes are spheres of radius 1e6.  Left inside the SAH build they stretch the binning domain and can end up deep in a mesh's
+    # subtree (every node above them inherits a 3e6-wide box): the host builder keeps primitives whose extent exceeds 1024 x the geometric
+    # mean extent out of the build and chains them above its root, like the device builder does (bvh_fast.cpp, bvh_device.cu).
+    sc = pb.Scene.load(f"scenes/{name}.yml", width=64, height=64)
+    sc.build_bvh()
+    info = sc.info
+    assert info["giant_prims"] == giants
+    # the chain adds one level per giant above a tree that is balanced enough for the 64-entry traversal stack
+    assert giants < info["fast_depth"] <= 60
+    assert info["hidden_prims"] == 0 and info["fast_nodes"] >= 1
+
+
+def test_host_builder_leaves_ordinary_scenes_alone(pb):
+    # no giant among comparable primitives: a soup of triangles and unit-sized spheres keeps them all in the SAH build;
+    # one sphere of radius 1e6 among them is the only one chained
+    desc = _soup_desc(np.random.default_rng(5), 400, 6, flat=0)
+    sc = pb.Scene(desc)
+    assert sc.build_bvh(reference=False)["giant_prims"] == 0
+    desc["objects"].append({"shape": "Sphere", "center": [0.0, -1e6, 0.0], "radius": 1e6,
+                            "material": {"type": "Lambertian", "albedo": {"type": "Rgb", "rgb": [0.5, 0.5, 0.5]}}})
+    sc = pb.Scene(desc)
+    info = sc.build_bvh(reference=False)
+    assert info["giant_prims"] == 1 and info["fast_depth"] <= 60
